@@ -1,0 +1,460 @@
+// te_gemm.cu -- batched FP64 tile update  C_i = alpha op(A_i) op(B_i) + beta C_i
+//
+// One persistent launch per block outer product per device.  Replaces the
+// cublasDgemmBatched / cublasDsyrk calls behind SLATE's
+// internal::gemm/herk/syrk<Target::Devices>
+// (reference: src/internal/internal_gemm.cc:355-518, internal_herk.cc:351-535,
+//  blaspp/src/device_batch_gemm.cc:25-142).
+//
+// Design (B200, sm_100a)
+//   * tcgen05/TMEM has no FP64 kind, so the FP64 tensor path is the
+//     warp-synchronous DMMA.8x8x4 (mma.sync.m8n8k4.f64).
+//   * CTA tile 128x128, 8 warps, warp tile 64(m) x 32(n): 32 accumulator
+//     fragments (128 registers) per thread, 12 LDS.64 per 32 DMMA.
+//   * operands staged GMEM -> SMEM by 16-byte cp.async (.cg, L2 only) through
+//     a 4-stage ring of K=16 slices; +4 padding per row makes every
+//     64-bit fragment load bank-conflict free for both storage orders.
+//   * persistent CTAs (one per SM) walk a flat list of (tile, 128x128 block)
+//     work items in the order the host laid the descriptors out (the host
+//     orders them for L2 reuse of the A/B panels); the cp.async ring runs
+//     ACROSS work items, so the next block's first slices are in flight while
+//     the current block's epilogue reads/writes C.
+//   * ragged edges (m, n, k not multiples of the tile) are zero-filled by
+//     cp.async src-size and masked in the epilogue; odd leading dimensions /
+//     8-byte aligned tiles fall back to 8-byte cp.async per element.
+//   * epilogue in registers: each lane owns two consecutive rows of one
+//     column (the MMA is issued on C^T), so C is read/written as 16-byte
+//     vectors forming 64-byte column segments per quad.
+#include "te_common.cuh"
+
+namespace te {
+
+constexpr int BM = 128;
+constexpr int BN = 128;
+constexpr int KC = 16;
+constexpr int STAGES = 5;
+constexpr int NCONSUMERS = 8;                      // consumer warps
+constexpr int NPRODUCERS = 4;                      // producer warps (one warpgroup)
+constexpr int NTHREADS = (NCONSUMERS + NPRODUCERS) * 32;
+constexpr int REGS_PRODUCER = 56;                  // setmaxnreg budgets: 56*128 + 224*256
+constexpr int REGS_CONSUMER = 224;                 //   = 168*384 (the launch allocation)
+constexpr int LD_MN = BM + 4;            // row stride (doubles) of an [k][mn] slice
+constexpr int LD_K = KC + 4;             // row stride (doubles) of an [mn][k] slice
+constexpr int SLICE_MN = KC * LD_MN;     // 2112 doubles
+constexpr int SLICE_K = BM * LD_K;       // 2560 doubles
+constexpr int SLICE = (SLICE_MN > SLICE_K) ? SLICE_MN : SLICE_K;
+constexpr int SMEM_BYTES = STAGES * 2 * SLICE * (int)sizeof(double) + 2 * STAGES * 8;
+
+struct GemmParams {
+    const te_tile_desc* desc;      // device array (batched mode)
+    int64_t total_work;            // count * blocks_per_tile
+    int32_t nbm, nbn;              // 128-blocks per tile in m and n
+    double alpha, beta;
+    int32_t inline_count;          // > 0: use inl[] instead of desc
+    te_tile_desc inl[TE_MAX_INLINE_DESC];
+};
+
+// One 128x128 block of one tile.
+struct Item {
+    const double* a;
+    const double* b;
+    double* c;
+    int m, n, k;                   // extents of this block (m, n may exceed 128: remaining)
+    int lda, ldb, ldc;
+    int flags;
+    int m0, n0;                    // offset of the block inside its tile
+    bool a16, b16, c16;            // 16-byte path usable
+};
+
+template <bool INL>
+__device__ __forceinline__ bool decode(const GemmParams& p, int64_t w, Item& it)
+{
+    const int bpt = p.nbm * p.nbn;
+    const int64_t t = w / bpt;
+    const int sub = (int)(w - t * bpt);
+    const int sn = sub / p.nbm;
+    const int sm = sub - sn * p.nbm;
+    const te_tile_desc* d = INL ? &p.inl[t] : &p.desc[t];
+    const int m = d->m, n = d->n;
+    const int m0 = sm * BM, n0 = sn * BN;
+    if (m0 >= m || n0 >= n)
+        return false;
+    const int flags = d->flags;
+    if ((flags & TE_TILE_LOWER) && (m0 + BM - 1 < n0))
+        return false;
+    if ((flags & TE_TILE_UPPER) && (n0 + BN - 1 < m0))
+        return false;
+    it.m = m - m0;
+    it.n = n - n0;
+    it.k = d->k;
+    it.lda = d->lda;
+    it.ldb = d->ldb;
+    it.ldc = d->ldc;
+    it.flags = flags;
+    it.m0 = m0;
+    it.n0 = n0;
+    it.a = (const double*)d->a;
+    it.b = (const double*)d->b;
+    it.c = (double*)d->c;
+    it.a16 = ((((uintptr_t)it.a) & 15) == 0) && ((it.lda & 1) == 0);
+    it.b16 = ((((uintptr_t)it.b) & 15) == 0) && ((it.ldb & 1) == 0);
+    it.c16 = ((((uintptr_t)it.c) & 15) == 0) && ((it.ldc & 1) == 0);
+    return true;
+}
+
+// Walks the work list of this CTA: w = blockIdx.x, += gridDim.x, skipping
+// blocks that fall outside their (ragged / triangular) tile.
+template <bool INL>
+struct Walker {
+    int64_t w;
+    int nk;        // K slices of the current item
+    bool valid;
+    Item it;
+
+    __device__ __forceinline__ void seek(const GemmParams& p)
+    {
+        valid = false;
+        while (w < p.total_work) {
+            if (decode<INL>(p, w, it)) {
+                valid = true;
+                nk = (it.k + KC - 1) / KC;
+                return;
+            }
+            w += gridDim.x;
+        }
+    }
+    __device__ __forceinline__ void start(const GemmParams& p)
+    {
+        w = blockIdx.x;
+        seek(p);
+    }
+    __device__ __forceinline__ void next_item(const GemmParams& p)
+    {
+        w += gridDim.x;
+        seek(p);
+    }
+};
+
+// Stage one K slice of one operand with the 128 threads of the producer warpgroup.
+// `g` points at element (x0, k0) of the operand; x_rem / k_rem are the valid
+// extents from there (anything beyond is zero-filled).
+//   KMAJOR == false: global (x, kk) at g[x + kk*ld]  -> smem [kk][LD_MN]
+//   KMAJOR == true : global (x, kk) at g[kk + x*ld]  -> smem [x][LD_K]
+template <bool KMAJOR>
+__device__ __forceinline__ void load_slice(double* s, const double* g, int ld,
+                                           int x_rem, int k_rem, bool al16, int ptid)
+{
+    const uint32_t sbase = smem_u32(s);
+    constexpr int NCHUNK = BM * KC / 2;          // 16-byte chunks per slice
+#pragma unroll
+    for (int i = 0; i < NCHUNK / (NPRODUCERS * 32); ++i) {
+        const int c = ptid + i * (NPRODUCERS * 32);
+        int row, col, nv;
+        uint32_t soff;
+        if (!KMAJOR) {
+            row = c >> 6;              // kk
+            col = (c & 63) * 2;        // x
+            nv = (row < k_rem) ? min(max(x_rem - col, 0), 2) : 0;
+            soff = (uint32_t)(row * LD_MN + col);
+        }
+        else {
+            row = c >> 3;              // x
+            col = (c & 7) * 2;         // kk
+            nv = (row < x_rem) ? min(max(k_rem - col, 0), 2) : 0;
+            soff = (uint32_t)(row * LD_K + col);
+        }
+        const double* src = (nv > 0) ? (g + ((int64_t)row * ld + col)) : g;
+        const uint32_t dst = sbase + soff * 8u;
+        if (al16) {
+            cp_async16(dst, src, nv * 8);
+        }
+        else {
+            cp_async8(dst, src, nv > 0 ? 8 : 0);
+            cp_async8(dst + 8u, (nv > 1) ? (src + 1) : src, nv > 1 ? 8 : 0);
+        }
+    }
+}
+
+// Warp roles: warps 0..7 (two warpgroups) consume (LDS + DMMA + epilogue), warps
+// 8..11 (one warpgroup) produce (cp.async into the ring, L2 prefetch of the C
+// block).  setmaxnreg moves registers from the producers to the consumers.
+// full[s] completes when the 128 producer threads' copies of stage s have
+// landed; empty[s] when the 8 consumer warps have finished reading it.  There
+// is no CTA-wide barrier in the loop.
+template <bool TA, bool TB, bool INL>
+__global__ void __launch_bounds__(NTHREADS, 1)
+dgemm_tiles_kernel(const __grid_constant__ GemmParams p)
+{
+    extern __shared__ __align__(16) double smem[];
+    double* sA = smem;                       // STAGES slices
+    double* sB = smem + STAGES * SLICE;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * STAGES * SLICE);
+    const uint32_t full0 = smem_u32(bars);
+    const uint32_t empty0 = smem_u32(bars + STAGES);
+
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
+    const int warp = tid >> 5;
+
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(full0 + 8 * s, NPRODUCERS * 32);
+            mbar_init(empty0 + 8 * s, NCONSUMERS);
+        }
+    }
+    __syncthreads();
+
+    // op(A) = N: stored m x k, m contiguous -> [k][mn].  op(A) = T: k contiguous -> [mn][k].
+    // op(B) = N: stored k x n, k contiguous -> [mn][k].  op(B) = T: n contiguous -> [k][mn].
+    constexpr bool A_KMAJOR = TA;
+    constexpr bool B_KMAJOR = !TB;
+
+    Walker<INL> wk;
+    wk.start(p);
+    int stage = 0;
+    uint32_t phase = 0;
+
+    if (warp >= NCONSUMERS) {
+        // ------------------------------ producers -----------------------------
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" :: "n"(REGS_PRODUCER));
+        const int ptid = tid - NCONSUMERS * 32;
+#pragma unroll 1
+        while (wk.valid) {
+            const Item& it = wk.it;
+            if (wk.nk > 0) {
+                if (p.beta != 0.0) {
+                    // pull this block of C towards L2 while the main loop runs
+                    const int rows = min(it.m, BM), cols = min(it.n, BN);
+                    const double* cblk = it.c + (int64_t)it.n0 * it.ldc + it.m0;
+                    for (int q = ptid; q < cols * 8; q += NPRODUCERS * 32) {
+                        const int col = q >> 3, seg = (q & 7) * 16;
+                        if (seg < rows)
+                            prefetch_l2(cblk + (int64_t)col * it.ldc + seg);
+                    }
+                }
+#pragma unroll 1
+                for (int kc = 0; kc < wk.nk; ++kc) {
+                    const int k0 = kc * KC;
+                    const int k_rem = it.k - k0;
+                    const double* ga = A_KMAJOR
+                        ? it.a + (int64_t)it.m0 * it.lda + k0
+                        : it.a + (int64_t)k0 * it.lda + it.m0;
+                    const double* gb = B_KMAJOR
+                        ? it.b + (int64_t)it.n0 * it.ldb + k0
+                        : it.b + (int64_t)k0 * it.ldb + it.n0;
+                    mbar_wait(empty0 + 8 * stage, phase ^ 1);
+                    load_slice<A_KMAJOR>(sA + stage * SLICE, ga, it.lda, it.m, k_rem, it.a16, ptid);
+                    load_slice<B_KMAJOR>(sB + stage * SLICE, gb, it.ldb, it.n, k_rem, it.b16, ptid);
+                    cp_async_mbar_arrive(full0 + 8 * stage);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+            wk.next_item(p);
+        }
+        cp_async_wait_all();
+        return;
+    }
+
+    // -------------------------------- consumers --------------------------------
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" :: "n"(REGS_CONSUMER));
+    const int g = lane >> 2;                 // 0..7
+    const int t = lane & 3;                  // 0..3
+    const int wm = (warp & 1) * 64;          // warp tile origin in the block
+    const int wn = (warp >> 1) * 32;
+
+#pragma unroll 1
+    while (wk.valid) {
+        double acc[4][8][2];
+#pragma unroll
+        for (int in = 0; in < 4; ++in)
+#pragma unroll
+            for (int im = 0; im < 8; ++im)
+                acc[in][im][0] = acc[in][im][1] = 0.0;
+
+        const int nk = wk.nk;
+#pragma unroll 1
+        for (int kc = 0; kc < nk; ++kc) {
+            mbar_wait(full0 + 8 * stage, phase);
+            const double* a_s = sA + stage * SLICE;
+            const double* b_s = sB + stage * SLICE;
+#pragma unroll
+            for (int k4 = 0; k4 < KC / 4; ++k4) {
+                double af[8], bf[4];
+                const int kk = k4 * 4 + t;
+#pragma unroll
+                for (int im = 0; im < 8; ++im) {
+                    const int x = wm + im * 8 + g;
+                    af[im] = A_KMAJOR ? a_s[x * LD_K + kk] : a_s[kk * LD_MN + x];
+                }
+#pragma unroll
+                for (int in = 0; in < 4; ++in) {
+                    const int x = wn + in * 8 + g;
+                    bf[in] = B_KMAJOR ? b_s[x * LD_K + kk] : b_s[kk * LD_MN + x];
+                }
+#pragma unroll
+                for (int in = 0; in < 4; ++in)
+#pragma unroll
+                    for (int im = 0; im < 8; ++im)
+                        dmma884(acc[in][im][0], acc[in][im][1], bf[in], af[im]);
+            }
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(empty0 + 8 * stage);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+
+        // ---- epilogue: lane owns rows (2t, 2t+1) of column g in each 8x8 ----
+        {
+            const Item& it = wk.it;
+            const double alpha = p.alpha, beta = p.beta;
+            const bool lower = (it.flags & TE_TILE_LOWER) != 0;
+            const bool upper = (it.flags & TE_TILE_UPPER) != 0;
+            double* cblk = it.c + (int64_t)it.n0 * it.ldc + it.m0;
+#pragma unroll
+            for (int in = 0; in < 4; ++in) {
+                const int col = wn + in * 8 + g;
+                if (col >= it.n)
+                    continue;
+                double* ccol = cblk + (int64_t)col * it.ldc;
+                const int gcol = it.n0 + col;          // column inside the tile
+#pragma unroll
+                for (int im = 0; im < 8; ++im) {
+                    const int row = wm + im * 8 + 2 * t;
+                    if (row >= it.m)
+                        continue;
+                    const int grow = it.m0 + row;
+                    bool ok0 = true, ok1 = (row + 1 < it.m);
+                    if (lower) { ok0 = ok0 && (grow >= gcol); ok1 = ok1 && (grow + 1 >= gcol); }
+                    if (upper) { ok0 = ok0 && (grow <= gcol); ok1 = ok1 && (grow + 1 <= gcol); }
+                    double v0 = alpha * acc[in][im][0];
+                    double v1 = alpha * acc[in][im][1];
+                    double* dst = ccol + row;
+                    if (ok0 && ok1 && it.c16) {
+                        if (beta != 0.0) {
+                            const double2 old = *reinterpret_cast<const double2*>(dst);
+                            v0 += beta * old.x;
+                            v1 += beta * old.y;
+                        }
+                        *reinterpret_cast<double2*>(dst) = make_double2(v0, v1);
+                    }
+                    else {
+                        if (ok0) {
+                            if (beta != 0.0) v0 += beta * dst[0];
+                            dst[0] = v0;
+                        }
+                        if (ok1) {
+                            if (beta != 0.0) v1 += beta * dst[1];
+                            dst[1] = v1;
+                        }
+                    }
+                }
+            }
+        }
+        wk.next_item(p);
+    }
+}
+
+// ---- host side ----------------------------------------------------------------
+template <bool TA, bool TB, bool INL>
+static int launch(int device, cudaStream_t stream, const GemmParams& p)
+{
+    static bool configured[64] = {};
+    auto kern = dgemm_tiles_kernel<TA, TB, INL>;
+    if (device < 64 && !configured[device]) {
+        TE_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           SMEM_BYTES));
+        configured[device] = true;
+    }
+    const int sms = num_sms(device);
+    const int64_t grid = p.total_work < sms ? p.total_work : sms;
+    kern<<<(unsigned)grid, NTHREADS, SMEM_BYTES, stream>>>(p);
+    TE_CUDA_CHECK(cudaGetLastError());
+    return TE_OK;
+}
+
+template <bool INL>
+static int dispatch(int device, cudaStream_t stream, int opa, int opb, const GemmParams& p)
+{
+    const bool ta = (opa != TE_OP_N), tb = (opb != TE_OP_N);
+    if (!ta && !tb) return launch<false, false, INL>(device, stream, p);
+    if (!ta &&  tb) return launch<false, true,  INL>(device, stream, p);
+    if ( ta && !tb) return launch<true,  false, INL>(device, stream, p);
+    return launch<true, true, INL>(device, stream, p);
+}
+
+static bool op_ok(int op) { return op == TE_OP_N || op == TE_OP_T || op == TE_OP_C; }
+
+int dgemm_batched(int device, cudaStream_t stream, int opa, int opb, double alpha, double beta,
+                  const te_tile_desc* desc, int64_t count, int32_t max_m, int32_t max_n)
+{
+    GemmParams p;
+    p.desc = desc;
+    p.nbm = (max_m + BM - 1) / BM;
+    p.nbn = (max_n + BN - 1) / BN;
+    p.total_work = count * p.nbm * p.nbn;
+    p.alpha = alpha;
+    p.beta = beta;
+    p.inline_count = 0;
+    return dispatch<false>(device, stream, opa, opb, p);
+}
+
+int dgemm_inline(int device, cudaStream_t stream, int opa, int opb, double alpha, double beta,
+                 const te_tile_desc* desc_host, int count)
+{
+    GemmParams p;
+    p.desc = nullptr;
+    int32_t max_m = 0, max_n = 0;
+    for (int i = 0; i < count; ++i) {
+        p.inl[i] = desc_host[i];
+        if (desc_host[i].m > max_m) max_m = desc_host[i].m;
+        if (desc_host[i].n > max_n) max_n = desc_host[i].n;
+    }
+    p.nbm = (max_m + BM - 1) / BM;
+    p.nbn = (max_n + BN - 1) / BN;
+    p.total_work = (int64_t)count * p.nbm * p.nbn;
+    p.alpha = alpha;
+    p.beta = beta;
+    p.inline_count = count;
+    return dispatch<true>(device, stream, opa, opb, p);
+}
+
+}  // namespace te
+
+extern "C" int te_gemm_batched(int device, void* stream, int dtype, int opa, int opb,
+                               const void* alpha, const void* beta,
+                               const te_tile_desc* desc, int64_t count,
+                               int32_t max_m, int32_t max_n)
+{
+    if (!alpha || !beta || count < 0 || max_m < 0 || max_n < 0 ||
+        !te::op_ok(opa) || !te::op_ok(opb) || (count > 0 && !desc))
+        return TE_ERR_ARG;
+    if (count == 0 || max_m == 0 || max_n == 0)
+        return TE_OK;
+    int st = te::set_device(device);
+    if (st != TE_OK) return st;
+    if (dtype == TE_F64) {
+        return te::dgemm_batched(device, (cudaStream_t)stream, opa, opb,
+                                 *(const double*)alpha, *(const double*)beta,
+                                 desc, count, max_m, max_n);
+    }
+    return TE_ERR_UNSUPPORTED;
+}
+
+extern "C" int te_gemm_inline(int device, void* stream, int dtype, int opa, int opb,
+                              const void* alpha, const void* beta,
+                              const te_tile_desc* desc_host, int count)
+{
+    if (!alpha || !beta || count < 0 || count > TE_MAX_INLINE_DESC ||
+        !te::op_ok(opa) || !te::op_ok(opb) || (count > 0 && !desc_host))
+        return TE_ERR_ARG;
+    if (count == 0)
+        return TE_OK;
+    int st = te::set_device(device);
+    if (st != TE_OK) return st;
+    if (dtype == TE_F64) {
+        return te::dgemm_inline(device, (cudaStream_t)stream, opa, opb,
+                                *(const double*)alpha, *(const double*)beta,
+                                desc_host, count);
+    }
+    return TE_ERR_UNSUPPORTED;
+}
