@@ -55,6 +55,59 @@ const char* te_version(void);
 int te_device_count(void);
 
 /* ------------------------------------------------------------------------
+ * Streams, events, copies.  Stand in for blas::Queue and blas::device_memcpy /
+ * device_malloc (blaspp/include/blas/device.hh:445-726,
+ * blaspp/src/device_queue.cc), i.e. MatrixStorage::compute_queue / comm_queue
+ * (include/slate/internal/MatrixStorage.hh:198-245, 574-626).
+ * ---------------------------------------------------------------------- */
+enum { TE_COPY_H2D = 1, TE_COPY_D2H = 2, TE_COPY_D2D = 3, TE_COPY_DEFAULT = 4 };
+
+int te_stream_create(int device, int high_priority, void** stream);
+int te_stream_destroy(int device, void* stream);
+int te_stream_sync(int device, void* stream);
+int te_device_sync(int device);
+int te_event_create(int device, int timing, void** event);
+int te_event_destroy(void* event);
+int te_event_record(void* event, void* stream);
+int te_stream_wait_event(void* stream, void* event);
+int te_event_sync(void* event);
+int te_event_elapsed_ms(void* start, void* stop, float* ms);
+
+int te_device_malloc(int device, size_t bytes, void** ptr);
+int te_device_free(int device, void* ptr);
+int te_device_mem_info(int device, size_t* free_bytes, size_t* total_bytes);
+int te_host_alloc_pinned(size_t bytes, void** ptr);
+int te_host_free_pinned(void* ptr);
+int te_host_register(void* ptr, size_t bytes);
+int te_host_unregister(void* ptr);
+int te_memcpy_async(void* dst, const void* src, size_t bytes, int kind, void* stream);
+/* column-major tile copy: `height` columns of `width_bytes`, pitches in bytes
+ * (Tile::copyData, include/slate/Tile.hh:971-1042) */
+int te_memcpy2d_async(void* dst, size_t dpitch, const void* src, size_t spitch,
+                      size_t width_bytes, size_t height, int kind, void* stream);
+int te_memset_async(void* dst, int value, size_t bytes, void* stream);
+
+/* ------------------------------------------------------------------------
+ * Device-tile memory pool: fixed-size blocks (sizeof(T)*mb*nb, rounded up to
+ * 256 bytes) on one device.  Replaces slate::Memory
+ * (include/slate/internal/Memory.hh:29-101, src/core/Memory.cc:17-218):
+ *   te_pool_reserve  <-> Memory::addDeviceBlocks  (ONE cudaMalloc slab per call)
+ *   te_pool_alloc    <-> Memory::alloc  (pops; grows by one block when empty)
+ *   te_pool_free     <-> Memory::free
+ *   te_pool_stats    <-> Memory::available / capacity (allocated = cap - avail)
+ *   te_pool_clear    <-> Memory::clearDeviceBlocks
+ * Thread-safe (the reference uses omp critical(slate_memory)).
+ * ---------------------------------------------------------------------- */
+typedef struct te_pool te_pool;
+int te_pool_create(int device, size_t block_bytes, te_pool** pool);
+int te_pool_reserve(te_pool* pool, int64_t nblocks);
+int te_pool_alloc(te_pool* pool, void** block);
+int te_pool_free(te_pool* pool, void* block);
+int te_pool_stats(te_pool* pool, size_t* available, size_t* capacity, size_t* block_bytes);
+int te_pool_clear(te_pool* pool);
+int te_pool_destroy(te_pool* pool);
+
+/* ------------------------------------------------------------------------
  * Batched tile update:  C_i = alpha * op(A_i) * op(B_i) + beta * C_i
  *
  * One launch covers a whole block outer product on one device, ragged edge
@@ -105,6 +158,70 @@ int te_gemm_batched(int device, void* stream, int dtype, int opa, int opb,
 int te_gemm_inline(int device, void* stream, int dtype, int opa, int opb,
                    const void* alpha, const void* beta,
                    const te_tile_desc* desc_host, int count);
+
+/* ------------------------------------------------------------------------
+ * Cholesky of one tile, in place:  A = L L^H (lower) or U^H U (upper).
+ *
+ * Replaces lapack::potrf(uplo, n, A, lda, info, queue) -> cusolverDnXpotrf
+ *   src/internal/internal_potrf.cc:57-81, lapackpp/src/cuda/cuda_potrf.cc:128-171.
+ * Only the `uplo` triangle of A is read or written.  *info_dev (DEVICE int) is
+ * set on the stream to 0, or to the 1-based index of the first pivot that is
+ * not positive; there is no host synchronisation (the reference copies info
+ * back and syncs every step: internal_potrf.cc:75-78).
+ * scratch: DEVICE memory of at least te_potrf_scratch_bytes(dtype) bytes,
+ * private to this call until the stream has passed it (inverse of the current
+ * diagonal block).
+ * ---------------------------------------------------------------------- */
+size_t te_potrf_scratch_bytes(int dtype);
+int te_potrf_tile(int device, void* stream, int dtype, int uplo, int n, void* A, int lda,
+                  int* info_dev, void* scratch, size_t scratch_bytes);
+
+/* ------------------------------------------------------------------------
+ * Batched triangular solve with ONE triangular tile A shared by the batch:
+ *   side R:  B_i = alpha B_i op(A)^-1   (B_i is m_i x na)
+ *   side L:  B_i = alpha op(A)^-1 B_i   (B_i is na x n_i)
+ *
+ * Replaces blas::batch::trsm -> cublas{D,Z}trsmBatched with the A pointer
+ * replicated (src/internal/internal_trsm.cc:132-261,
+ * src/internal/internal_batch.hh:251-258, blaspp/src/device_batch_trsm.cc:71-111).
+ * Method: invert the diagonal blocks of A, then block substitution as tile
+ * GEMMs on the DMMA kernel.  b_desc is a DEVICE array; scratch is DEVICE
+ * memory of te_trsm_scratch_bytes(dtype, na, count) bytes, private to the call
+ * until the stream has passed it.
+ * ---------------------------------------------------------------------- */
+typedef struct te_trsm_desc {
+    void*   b;
+    int32_t m, n;            /* extents of B_i (the side-determined one must equal na) */
+    int32_t ldb;
+    int32_t reserved;
+} te_trsm_desc;              /* 24 bytes */
+
+size_t te_trsm_scratch_bytes(int dtype, int na, int64_t count);
+int te_trsm_batched(int device, void* stream, int dtype, int side, int uplo, int opa, int diag,
+                    const void* alpha, const void* A, int lda, int na,
+                    const te_trsm_desc* b_desc, int64_t count, int32_t max_m, int32_t max_n,
+                    void* scratch, size_t scratch_bytes);
+
+/* ------------------------------------------------------------------------
+ * Harness kernels around the hot path (inputs and residual checks).
+ *
+ * te_matgen_tile reproduces matgen bit for bit on the device: entry (i, j) of
+ * the tile is Philox-2x64-10 keyed by `seed` at counter (i + ioff, j + joff)
+ * (matgen/random.cc:53-159; dist 1 = uniform [0,1), 2 = uniform (-1,1));
+ * diag_add is added where i + ioff == j + joff ("rand_dominant",
+ * matgen/generate_type_rand.hh:70-78).  te_tile_add is B = alpha A + beta B
+ * (src/cuda/device_geadd.cu); te_tile_sumsq adds sum |a_ij|^2 over mask
+ * (0 full, 1 lower, 2 upper, 3 strictly lower) to *accum_dev;
+ * te_tile_keep_triangle zeroes the other strict triangle (device_tzset.cu).
+ * ---------------------------------------------------------------------- */
+int te_matgen_tile(int device, void* stream, int dtype, int dist, int64_t seed, int m, int n,
+                   int64_t ioff, int64_t joff, void* A, int64_t lda, double diag_add);
+int te_tile_add(int device, void* stream, int dtype, int m, int n, double alpha, const void* A,
+                int64_t lda, double beta, void* B, int64_t ldb);
+int te_tile_sumsq(int device, void* stream, int dtype, int mask, int m, int n, const void* A,
+                  int64_t lda, double* accum_dev);
+int te_tile_keep_triangle(int device, void* stream, int dtype, int uplo, int m, int n, void* A,
+                          int64_t lda);
 
 /* ------------------------------------------------------------------------
  * FP64 issue-rate microbenchmarks (the roofline denominators).

@@ -25,6 +25,14 @@ class TileDesc(C.Structure):
 
 assert C.sizeof(TileDesc) == 56
 
+
+class TrsmDesc(C.Structure):
+    _fields_ = [("b", C.c_void_p), ("m", C.c_int32), ("n", C.c_int32),
+                ("ldb", C.c_int32), ("reserved", C.c_int32)]
+
+
+assert C.sizeof(TrsmDesc) == 24
+
 _lib = None
 
 
@@ -48,6 +56,27 @@ def lib():
     L.te_gemm_inline.restype = C.c_int
     L.te_gemm_inline.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    vp, i32, i64, sz = C.c_void_p, C.c_int32, C.c_int64, C.c_size_t
+    L.te_potrf_scratch_bytes.restype = sz
+    L.te_potrf_scratch_bytes.argtypes = [C.c_int]
+    L.te_potrf_tile.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, vp, vp, sz]
+    L.te_trsm_scratch_bytes.restype = sz
+    L.te_trsm_scratch_bytes.argtypes = [C.c_int, C.c_int, i64]
+    L.te_trsm_batched.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp,
+                                  C.c_int, C.c_int, vp, i64, i32, i32, vp, sz]
+    L.te_matgen_tile.argtypes = [C.c_int, vp, C.c_int, C.c_int, i64, C.c_int, C.c_int, i64, i64,
+                                 vp, i64, C.c_double]
+    L.te_tile_add.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_double, vp, i64,
+                              C.c_double, vp, i64]
+    L.te_tile_sumsq.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, i64, vp]
+    L.te_tile_keep_triangle.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, i64]
+    L.te_pool_create.argtypes = [C.c_int, sz, C.POINTER(vp)]
+    L.te_pool_reserve.argtypes = [vp, i64]
+    L.te_pool_alloc.argtypes = [vp, C.POINTER(vp)]
+    L.te_pool_free.argtypes = [vp, vp]
+    L.te_pool_stats.argtypes = [vp, C.POINTER(sz), C.POINTER(sz), C.POINTER(sz)]
+    L.te_pool_clear.argtypes = [vp]
+    L.te_pool_destroy.argtypes = [vp]
     L.te_peak_fp64.restype = C.c_int
     L.te_peak_fp64.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]
     _lib = L

@@ -1,0 +1,164 @@
+// te_aux.cu -- small tile kernels used by the harness around the hot path:
+// the matgen generator (so device-origin matrices need no 32 GiB host staging),
+// tile add / sum of squares / triangle masking for the residual checks.
+//
+// Reference counterparts: matgen/random.cc:53-159 (generator),
+// src/cuda/device_geadd.cu, device_genorm.cu, device_tzset.cu (aux tile kernels).
+#include "te_common.cuh"
+
+namespace te {
+
+// matgen/random.cc:53-75: Philox-2x64, 10 rounds, counter (i, j), key = seed.
+__device__ __forceinline__ void philox_2x64(uint64_t c0, uint64_t c1, uint64_t key,
+                                            uint64_t& o0, uint64_t& o1)
+{
+    const uint64_t bump = 0xD2B74407B1CE6E93ull;
+    const uint64_t mult = 0x9E3779B97F4A7C15ull;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        if (r != 0) key += bump;
+        const uint64_t lo = c1 * mult;
+        const uint64_t hi = __umul64hi(c1, mult);
+        const uint64_t L = c0;
+        c0 = lo;
+        c1 = hi ^ key ^ L;
+    }
+    o0 = c0;
+    o1 = c1;
+}
+
+// matgen/random.cc:80-89
+__device__ __forceinline__ double bits_to_real(uint64_t b)
+{
+    return (double)(b >> 11) * (1.0 / 9007199254740992.0);
+}
+
+template <bool CPLX>
+__global__ void matgen_kernel(double* A, int64_t lda, int m, int n, int64_t ioff, int64_t joff,
+                              uint64_t seed, int dist, double diag_add)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= m || j >= n) return;
+    uint64_t b0, b1;
+    philox_2x64((uint64_t)(i + ioff), (uint64_t)(j + joff), seed, b0, b1);
+    double re = bits_to_real(b0), im = bits_to_real(b1);
+    if (dist == 2) { re = 2 * re - 1; im = 2 * im - 1; }
+    if (i + ioff == j + joff) re += diag_add;        // generate_type_rand.hh:70-78 (dominant)
+    if (CPLX) {
+        A[2 * (i + j * lda)] = re;
+        A[2 * (i + j * lda) + 1] = im;
+    }
+    else {
+        A[i + j * lda] = re;
+    }
+}
+
+// B = alpha A + beta B (real view: complex tiles pass 2m rows)
+__global__ void tile_add_kernel(int m, int n, double alpha, const double* A, int64_t lda,
+                                double beta, double* B, int64_t ldb)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= m || j >= n) return;
+    B[i + j * ldb] = alpha * A[i + j * lda] + beta * B[i + j * ldb];
+}
+
+// *accum += sum |a_ij|^2 over the masked part (mask 0 full, 1 lower incl. diag, 2 upper incl.
+// diag, 3 strictly lower).  esz = doubles per element.
+__global__ void tile_sumsq_kernel(int m, int n, int esz, int mask, const double* A, int64_t lda,
+                                  double* accum)
+{
+    double s = 0;
+    for (int j = blockIdx.y; j < n; j += gridDim.y) {
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) {
+            const bool in = (mask == 0) || (mask == 1 && i >= j) || (mask == 2 && i <= j) ||
+                            (mask == 3 && i > j);
+            if (in) {
+                for (int e = 0; e < esz; ++e) {
+                    const double v = A[esz * (i + j * lda) + e];
+                    s += v * v;
+                }
+            }
+        }
+    }
+    for (int off = 16; off > 0; off >>= 1)
+        s += __shfl_xor_sync(0xffffffffu, s, off);
+    if ((threadIdx.x & 31) == 0 && s != 0.0)
+        atomicAdd(accum, s);
+}
+
+// zero the strict upper (keep 1) or strict lower (keep 2) part of a tile
+__global__ void tile_keep_triangle_kernel(int m, int n, int esz, int keep, double* A, int64_t lda)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= m || j >= n) return;
+    const bool zero = (keep == 1) ? (i < j) : (i > j);
+    if (zero)
+        for (int e = 0; e < esz; ++e) A[esz * (i + j * lda) + e] = 0.0;
+}
+
+}  // namespace te
+
+extern "C" int te_matgen_tile(int device, void* stream, int dtype, int dist, int64_t seed,
+                              int m, int n, int64_t ioff, int64_t joff, void* A, int64_t lda,
+                              double diag_add)
+{
+    if (!A || m < 0 || n < 0 || (dist != 1 && dist != 2)) return TE_ERR_ARG;
+    if (m == 0 || n == 0) return TE_OK;
+    int st = te::set_device(device);
+    if (st != TE_OK) return st;
+    dim3 grid((m + 127) / 128, n);
+    if (dtype == TE_C64)
+        te::matgen_kernel<true><<<grid, 128, 0, (cudaStream_t)stream>>>(
+            (double*)A, lda, m, n, ioff, joff, (uint64_t)seed, dist, diag_add);
+    else
+        te::matgen_kernel<false><<<grid, 128, 0, (cudaStream_t)stream>>>(
+            (double*)A, lda, m, n, ioff, joff, (uint64_t)seed, dist, diag_add);
+    TE_CUDA_CHECK(cudaGetLastError());
+    return TE_OK;
+}
+
+extern "C" int te_tile_add(int device, void* stream, int dtype, int m, int n, double alpha,
+                           const void* A, int64_t lda, double beta, void* B, int64_t ldb)
+{
+    if (!A || !B || m < 0 || n < 0) return TE_ERR_ARG;
+    if (m == 0 || n == 0) return TE_OK;
+    int st = te::set_device(device);
+    if (st != TE_OK) return st;
+    const int esz = (dtype == TE_C64) ? 2 : 1;
+    dim3 grid((m * esz + 127) / 128, n);
+    te::tile_add_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(
+        m * esz, n, alpha, (const double*)A, lda * esz, beta, (double*)B, ldb * esz);
+    TE_CUDA_CHECK(cudaGetLastError());
+    return TE_OK;
+}
+
+extern "C" int te_tile_sumsq(int device, void* stream, int dtype, int mask, int m, int n,
+                             const void* A, int64_t lda, double* accum_dev)
+{
+    if (!A || !accum_dev || m < 0 || n < 0 || mask < 0 || mask > 3) return TE_ERR_ARG;
+    if (m == 0 || n == 0) return TE_OK;
+    int st = te::set_device(device);
+    if (st != TE_OK) return st;
+    dim3 grid((m + 127) / 128 > 8 ? 8 : (m + 127) / 128, n > 64 ? 64 : n);
+    te::tile_sumsq_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(
+        m, n, (dtype == TE_C64) ? 2 : 1, mask, (const double*)A, lda, accum_dev);
+    TE_CUDA_CHECK(cudaGetLastError());
+    return TE_OK;
+}
+
+extern "C" int te_tile_keep_triangle(int device, void* stream, int dtype, int uplo, int m, int n,
+                                     void* A, int64_t lda)
+{
+    if (!A || m < 0 || n < 0 || (uplo != TE_UPLO_LOWER && uplo != TE_UPLO_UPPER)) return TE_ERR_ARG;
+    if (m == 0 || n == 0) return TE_OK;
+    int st = te::set_device(device);
+    if (st != TE_OK) return st;
+    dim3 grid((m + 127) / 128, n);
+    te::tile_keep_triangle_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(
+        m, n, (dtype == TE_C64) ? 2 : 1, uplo == TE_UPLO_LOWER ? 1 : 2, (double*)A, lda);
+    TE_CUDA_CHECK(cudaGetLastError());
+    return TE_OK;
+}

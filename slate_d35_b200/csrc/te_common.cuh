@@ -112,3 +112,39 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
 #endif  // __CUDACC__
 
 }  // namespace te
+
+// ---- scalar helpers shared by the panel kernels (double / complex double) ----
+#ifdef __CUDACC__
+namespace te {
+
+struct zd { double x, y; };      // interleaved complex double
+
+__host__ __device__ __forceinline__ zd make_zd(double x, double y) { zd r; r.x = x; r.y = y; return r; }
+__device__ __forceinline__ zd operator+(zd a, zd b) { return make_zd(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ zd operator-(zd a, zd b) { return make_zd(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ zd operator-(zd a) { return make_zd(-a.x, -a.y); }
+__device__ __forceinline__ zd operator*(zd a, zd b)
+{
+    return make_zd(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+__device__ __forceinline__ zd operator*(zd a, double s) { return make_zd(a.x * s, a.y * s); }
+__device__ __forceinline__ zd conj_(zd a) { return make_zd(a.x, -a.y); }
+__device__ __forceinline__ double conj_(double a) { return a; }
+__device__ __forceinline__ double real_(zd a) { return a.x; }
+__device__ __forceinline__ double real_(double a) { return a; }
+__device__ __forceinline__ void set_real(zd& a, double r) { a.x = r; a.y = 0.0; }
+__device__ __forceinline__ void set_real(double& a, double r) { a = r; }
+template <typename T> __device__ __forceinline__ T zero_();
+template <> __device__ __forceinline__ double zero_<double>() { return 0.0; }
+template <> __device__ __forceinline__ zd zero_<zd>() { return make_zd(0.0, 0.0); }
+template <typename T> __device__ __forceinline__ T from_real(double r);
+template <> __device__ __forceinline__ double from_real<double>(double r) { return r; }
+template <> __device__ __forceinline__ zd from_real<zd>(double r) { return make_zd(r, 0.0); }
+__device__ __forceinline__ double shfl_xor_(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+__device__ __forceinline__ zd shfl_xor_(zd v, int m)
+{
+    return make_zd(__shfl_xor_sync(0xffffffffu, v.x, m), __shfl_xor_sync(0xffffffffu, v.y, m));
+}
+
+}  // namespace te
+#endif

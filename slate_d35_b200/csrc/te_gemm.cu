@@ -418,6 +418,30 @@ int dgemm_inline(int device, cudaStream_t stream, int opa, int opb, double alpha
     return dispatch<true>(device, stream, opa, opb, p);
 }
 
+// dtype dispatch used by the C ABI and by the panel code (te_panel.cu)
+int gemm_batched_any(int device, cudaStream_t stream, int dtype, int opa, int opb,
+                     const void* alpha, const void* beta, const te_tile_desc* desc,
+                     int64_t count, int32_t max_m, int32_t max_n)
+{
+    if (count == 0 || max_m == 0 || max_n == 0)
+        return TE_OK;
+    if (dtype == TE_F64)
+        return dgemm_batched(device, stream, opa, opb, *(const double*)alpha,
+                             *(const double*)beta, desc, count, max_m, max_n);
+    return TE_ERR_UNSUPPORTED;
+}
+
+int gemm_inline_any(int device, cudaStream_t stream, int dtype, int opa, int opb,
+                    const void* alpha, const void* beta, const te_tile_desc* desc_host, int count)
+{
+    if (count == 0)
+        return TE_OK;
+    if (dtype == TE_F64)
+        return dgemm_inline(device, stream, opa, opb, *(const double*)alpha,
+                            *(const double*)beta, desc_host, count);
+    return TE_ERR_UNSUPPORTED;
+}
+
 }  // namespace te
 
 extern "C" int te_gemm_batched(int device, void* stream, int dtype, int opa, int opb,
@@ -428,16 +452,10 @@ extern "C" int te_gemm_batched(int device, void* stream, int dtype, int opa, int
     if (!alpha || !beta || count < 0 || max_m < 0 || max_n < 0 ||
         !te::op_ok(opa) || !te::op_ok(opb) || (count > 0 && !desc))
         return TE_ERR_ARG;
-    if (count == 0 || max_m == 0 || max_n == 0)
-        return TE_OK;
     int st = te::set_device(device);
     if (st != TE_OK) return st;
-    if (dtype == TE_F64) {
-        return te::dgemm_batched(device, (cudaStream_t)stream, opa, opb,
-                                 *(const double*)alpha, *(const double*)beta,
-                                 desc, count, max_m, max_n);
-    }
-    return TE_ERR_UNSUPPORTED;
+    return te::gemm_batched_any(device, (cudaStream_t)stream, dtype, opa, opb, alpha, beta, desc,
+                                count, max_m, max_n);
 }
 
 extern "C" int te_gemm_inline(int device, void* stream, int dtype, int opa, int opb,
@@ -447,14 +465,8 @@ extern "C" int te_gemm_inline(int device, void* stream, int dtype, int opa, int 
     if (!alpha || !beta || count < 0 || count > TE_MAX_INLINE_DESC ||
         !te::op_ok(opa) || !te::op_ok(opb) || (count > 0 && !desc_host))
         return TE_ERR_ARG;
-    if (count == 0)
-        return TE_OK;
     int st = te::set_device(device);
     if (st != TE_OK) return st;
-    if (dtype == TE_F64) {
-        return te::dgemm_inline(device, (cudaStream_t)stream, opa, opb,
-                                *(const double*)alpha, *(const double*)beta,
-                                desc_host, count);
-    }
-    return TE_ERR_UNSUPPORTED;
+    return te::gemm_inline_any(device, (cudaStream_t)stream, dtype, opa, opb, alpha, beta,
+                               desc_host, count);
 }

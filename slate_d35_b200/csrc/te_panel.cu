@@ -1,0 +1,411 @@
+// te_panel.cu -- the panel (critical-path) kernels of the tiled Cholesky:
+// single-tile potrf and batched triangular solve, FP64 and complex-FP64.
+//
+// Replaces, on the Target::Devices path,
+//   lapack::potrf(uplo, n, A, lda, info, queue) -> cusolverDnXpotrf
+//       (reference: src/internal/internal_potrf.cc:57-81,
+//        lapackpp/src/cuda/cuda_potrf.cc:128-171)
+//   blas::batch::trsm -> cublas{D,Z}trsmBatched
+//       (reference: src/internal/internal_trsm.cc:132-261,
+//        blaspp/src/device_batch_trsm.cc:71-111).
+//
+// Structure: a tile is processed in diagonal blocks of IB columns.  One CTA
+// factors an IB x IB diagonal block in shared memory (right-looking Cholesky)
+// and also forms the inverse of its triangular factor; everything else -- the
+// solve of the block column below it, the symmetric trailing update, and all of
+// the batched triangular solve -- is then expressed as tile GEMMs and runs on
+// the DMMA kernel of te_gemm.cu (in place where the CTA tile covers the whole
+// block, which holds because IB <= 128).  `info` stays on the device: nothing
+// here synchronises with the host.
+#include "te_common.cuh"
+
+namespace te {
+
+// implemented in te_gemm.cu
+int gemm_batched_any(int device, cudaStream_t stream, int dtype, int opa, int opb,
+                     const void* alpha, const void* beta, const te_tile_desc* desc,
+                     int64_t count, int32_t max_m, int32_t max_n);
+int gemm_inline_any(int device, cudaStream_t stream, int dtype, int opa, int opb,
+                    const void* alpha, const void* beta, const te_tile_desc* desc_host, int count);
+
+constexpr int PANEL_THREADS = 512;
+
+template <typename T> struct PanelCfg;
+template <> struct PanelCfg<double> { static constexpr int IB = 128; };
+template <> struct PanelCfg<zd>     { static constexpr int IB = 64; };
+
+// One CTA.  Works on the n x n (n <= IB) triangular block at A (uplo given by
+// `upper`), held in shared memory as a LOWER matrix S (an upper block is loaded
+// conjugate-transposed and stored back the same way).
+//   do_potf2 != 0: S <- chol(S); failure at local pivot j sets *info = info_base + j + 1
+//                  (first failure wins; a non-zero *info on entry skips the block).
+//   always:        inv <- inverse of the triangular factor, dense IB-strided block in
+//                  the same orientation as A's storage (zeros in the other triangle).
+//   unit_diag:     the diagonal of the factor is taken as 1 (trtri-only mode).
+template <typename T, int IB>
+__global__ void __launch_bounds__(PANEL_THREADS)
+potf2_trtri_kernel(T* A, int lda, int upper, T* inv, int* info, int info_base,
+                   int do_potf2, int unit_diag, int64_t a_block_stride, int64_t inv_block_stride,
+                   int n_total)
+{
+    extern __shared__ __align__(16) unsigned char panel_smem[];
+    T* S = reinterpret_cast<T*>(panel_smem);               // [IB][IB+1]
+    T* xd = S + IB * (IB + 1);                             // [IB] diagonal of the inverse
+    __shared__ int s_fail;
+    constexpr int LD = IB + 1;
+    const int tid = threadIdx.x;
+
+    // batched over diagonal blocks (trtri-only mode): block b starts at (b*IB, b*IB)
+    A += (int64_t)blockIdx.x * a_block_stride;
+    inv += (int64_t)blockIdx.x * inv_block_stride;
+    const int n = min(IB, n_total - (int)blockIdx.x * IB);
+
+    if (do_potf2 && *info != 0)
+        return;
+    if (tid == 0) s_fail = 0;
+
+    for (int idx = tid; idx < n * n; idx += PANEL_THREADS) {
+        const int r = idx % n, c = idx / n;
+        const T v = A[r + (int64_t)c * lda];
+        if (!upper) { if (r >= c) S[r * LD + c] = v; }
+        else        { if (r <= c) S[c * LD + r] = conj_(v); }
+    }
+    __syncthreads();
+
+    if (do_potf2) {
+        for (int j = 0; j < n; ++j) {
+            const double d = real_(S[j * LD + j]);
+            if (!(d > 0.0)) {                              // also catches NaN
+                if (tid == 0) { s_fail = j + 1; }
+                break;                                     // uniform: every thread reads the same d
+            }
+            const double r = sqrt(d);
+            const double rinv = 1.0 / r;
+            __syncthreads();                               // everyone has read S[j][j]
+            for (int i = j + 1 + tid; i < n; i += PANEL_THREADS)
+                S[i * LD + j] = S[i * LD + j] * rinv;
+            if (tid == 0) set_real(S[j * LD + j], r);
+            __syncthreads();
+            const int rem = n - j - 1;
+            for (int idx = tid; idx < rem * rem; idx += PANEL_THREADS) {
+                const int i = idx % rem, c = idx / rem;
+                if (i >= c) {
+                    const int gi = j + 1 + i, gc = j + 1 + c;
+                    S[gi * LD + gc] = S[gi * LD + gc] - S[gi * LD + j] * conj_(S[gc * LD + j]);
+                }
+            }
+            __syncthreads();
+        }
+        __syncthreads();
+        if (s_fail != 0) {
+            if (tid == 0) *info = info_base + s_fail;
+            return;                                        // LAPACK leaves the tile partly factored
+        }
+    }
+
+    // ---- inverse of the lower factor: X = S^-1, X^T kept in the strict upper part ----
+    // row i of X:  X[i][j] = -(sum_{l=j}^{i-1} S[i][l] X[l][j]) / S[i][i],  X[i][i] = 1/S[i][i]
+    for (int i = tid; i < n; i += PANEL_THREADS) {
+        if (unit_diag) xd[i] = from_real<T>(1.0);
+        else {
+            // complex diagonal of a Cholesky factor is real; a general triangular block may not be
+            const T d = S[i * LD + i];
+            const double den = real_(d * conj_(d));
+            xd[i] = conj_(d) * (1.0 / den);
+        }
+    }
+    __syncthreads();
+    for (int i = 1; i < n; ++i) {
+        // 4 lanes per column j split the sum over l
+        const int j = tid >> 2, part = tid & 3;
+        T sum = zero_<T>();
+        if (j < i) {
+            for (int l = j + part; l < i; l += 4) {
+                const T x = (l == j) ? xd[j] : S[j * LD + l];      // X[l][j]
+                sum = sum + S[i * LD + l] * x;
+            }
+        }
+        sum = sum + shfl_xor_(sum, 1);
+        sum = sum + shfl_xor_(sum, 2);
+        if (j < i && part == 0)
+            S[j * LD + i] = -(sum * xd[i]);
+        __syncthreads();
+    }
+
+    // ---- write back ----
+    for (int idx = tid; idx < n * n; idx += PANEL_THREADS) {
+        const int r = idx % n, c = idx / n;
+        // factor, in A's own triangle only
+        if (do_potf2) {
+            if (!upper) { if (r >= c) A[r + (int64_t)c * lda] = S[r * LD + c]; }
+            else        { if (r <= c) A[r + (int64_t)c * lda] = conj_(S[c * LD + r]); }
+        }
+        // inverse, dense block with leading dimension IB
+        T v = zero_<T>();
+        if (!upper) {
+            if (r == c) v = xd[r];
+            else if (r > c) v = S[c * LD + r];                     // X[r][c]
+        }
+        else {
+            if (r == c) v = conj_(xd[r]);
+            else if (r < c) v = conj_(S[r * LD + c]);              // conj(X[c][r])
+        }
+        inv[r + c * IB] = v;
+    }
+}
+
+template <typename T>
+static int panel_smem_bytes()
+{
+    constexpr int IB = PanelCfg<T>::IB;
+    return (IB * (IB + 1) + IB) * (int)sizeof(T);
+}
+
+template <typename T>
+static int configure_panel_kernel(int device)
+{
+    static bool done[64] = {};
+    constexpr int IB = PanelCfg<T>::IB;
+    if (device < 64 && done[device]) return TE_OK;
+    TE_CUDA_CHECK(cudaFuncSetAttribute(potf2_trtri_kernel<T, IB>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       panel_smem_bytes<T>()));
+    if (device < 64) done[device] = true;
+    return TE_OK;
+}
+
+// ------------------------------- tile potrf ----------------------------------
+template <typename T>
+static int potrf_tile(int device, cudaStream_t stream, int dtype, int uplo, int n, T* A, int lda,
+                      int* info, T* scratch)
+{
+    constexpr int IB = PanelCfg<T>::IB;
+    int st = configure_panel_kernel<T>(device);
+    if (st != TE_OK) return st;
+    const int upper = (uplo == TE_UPLO_UPPER);
+    TE_CUDA_CHECK(cudaMemsetAsync(info, 0, sizeof(int), stream));
+    const double one[2] = {1.0, 0.0}, zero[2] = {0.0, 0.0}, mone[2] = {-1.0, 0.0};
+    for (int jb = 0; jb < n; jb += IB) {
+        const int ib = (n - jb < IB) ? n - jb : IB;
+        T* Ajj = A + jb + (int64_t)jb * lda;
+        potf2_trtri_kernel<T, IB><<<1, PANEL_THREADS, panel_smem_bytes<T>(), stream>>>(
+            Ajj, lda, upper, scratch, info, jb, 1, 0, 0, 0, ib);
+        TE_CUDA_CHECK(cudaGetLastError());
+        const int rem = n - jb - ib;
+        if (rem <= 0) break;
+        te_tile_desc d;
+        d.reserved = 0;
+        if (!upper) {
+            T* P = A + (jb + ib) + (int64_t)jb * lda;            // rem x ib, below the block
+            T* A22 = A + (jb + ib) + (int64_t)(jb + ib) * lda;
+            // P <- P * inv(L)^H   (in place: the CTA tile spans all ib columns)
+            d.a = P; d.b = scratch; d.c = P; d.m = rem; d.n = ib; d.k = ib;
+            d.lda = lda; d.ldb = IB; d.ldc = lda; d.flags = TE_TILE_GENERAL;
+            st = gemm_inline_any(device, stream, dtype, TE_OP_N, TE_OP_C, one, zero, &d, 1);
+            if (st != TE_OK) return st;
+            // A22 <- A22 - P P^H on the lower triangle
+            d.a = P; d.b = P; d.c = A22; d.m = rem; d.n = rem; d.k = ib;
+            d.lda = lda; d.ldb = lda; d.ldc = lda; d.flags = TE_TILE_LOWER | TE_TILE_HERMITIAN;
+            st = gemm_inline_any(device, stream, dtype, TE_OP_N, TE_OP_C, mone, one, &d, 1);
+            if (st != TE_OK) return st;
+        }
+        else {
+            T* P = A + jb + (int64_t)(jb + ib) * lda;            // ib x rem, right of the block
+            T* A22 = A + (jb + ib) + (int64_t)(jb + ib) * lda;
+            // P <- inv(U)^H * P   (in place: the CTA tile spans all ib rows)
+            d.a = scratch; d.b = P; d.c = P; d.m = ib; d.n = rem; d.k = ib;
+            d.lda = IB; d.ldb = lda; d.ldc = lda; d.flags = TE_TILE_GENERAL;
+            st = gemm_inline_any(device, stream, dtype, TE_OP_C, TE_OP_N, one, zero, &d, 1);
+            if (st != TE_OK) return st;
+            // A22 <- A22 - P^H P on the upper triangle
+            d.a = P; d.b = P; d.c = A22; d.m = rem; d.n = rem; d.k = ib;
+            d.lda = lda; d.ldb = lda; d.ldc = lda; d.flags = TE_TILE_UPPER | TE_TILE_HERMITIAN;
+            st = gemm_inline_any(device, stream, dtype, TE_OP_C, TE_OP_N, mone, one, &d, 1);
+            if (st != TE_OK) return st;
+        }
+    }
+    return TE_OK;
+}
+
+// ------------------------------- batched trsm --------------------------------
+struct TrsmPlan {
+    const te_trsm_desc* b;     // device, count entries
+    te_tile_desc* upd;         // device, nblk * count
+    te_tile_desc* mul;         // device, nblk * count
+    const void* A;
+    const void* inv;
+    int64_t count;
+    int lda, na, nblk, IB, esize;
+    int right, eff_lower, op_is_n;
+};
+
+// One thread per (step s, batch entry i): writes the update and multiply
+// descriptors of diagonal block blk(s), in processing order.
+__global__ void trsm_build_descs_kernel(TrsmPlan p)
+{
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (int64_t)p.nblk * p.count) return;
+    const int s = (int)(idx / p.count);
+    const int64_t i = idx - (int64_t)s * p.count;
+    // right: ascending when op(A) is upper; left: ascending when op(A) is lower
+    const bool ascending = p.right ? !p.eff_lower : p.eff_lower;
+    const int blk = ascending ? s : (p.nblk - 1 - s);
+    const int j0 = blk * p.IB;
+    const int ib = min(p.IB, p.na - j0);
+    const int l0 = ascending ? 0 : j0 + ib;          // start of the already-solved range
+    const int kk = ascending ? j0 : p.na - (j0 + ib);
+    const te_trsm_desc bd = p.b[i];
+    char* B = (char*)bd.b;
+    const char* A = (const char*)p.A;
+    const int64_t es = p.esize;
+    te_tile_desc u, m;
+    u.flags = m.flags = TE_TILE_GENERAL;
+    u.reserved = m.reserved = 0;
+    const char* invb = (const char*)p.inv + (int64_t)blk * p.IB * p.IB * es;
+    if (p.right) {
+        // B is m x na.  T = alpha B(:, blk) - X(:, solved) * M(solved, blk);  X(:, blk) = T * inv
+        u.c = B + (int64_t)j0 * bd.ldb * es;  u.ldc = bd.ldb;  u.m = bd.m;  u.n = ib;  u.k = kk;
+        u.a = B + (int64_t)l0 * bd.ldb * es;  u.lda = bd.ldb;
+        u.b = p.op_is_n ? A + ((int64_t)l0 + (int64_t)j0 * p.lda) * es
+                        : A + ((int64_t)j0 + (int64_t)l0 * p.lda) * es;
+        u.ldb = p.lda;
+        m.c = (void*)u.c;  m.ldc = bd.ldb;  m.a = u.c;  m.lda = bd.ldb;
+        m.b = invb;  m.ldb = p.IB;  m.m = bd.m;  m.n = ib;  m.k = ib;
+    }
+    else {
+        // B is na x n.  T = alpha B(blk, :) - M(blk, solved) * X(solved, :);  X(blk, :) = inv * T
+        u.c = B + (int64_t)j0 * es;  u.ldc = bd.ldb;  u.m = ib;  u.n = bd.n;  u.k = kk;
+        u.a = p.op_is_n ? A + ((int64_t)j0 + (int64_t)l0 * p.lda) * es
+                        : A + ((int64_t)l0 + (int64_t)j0 * p.lda) * es;
+        u.lda = p.lda;
+        u.b = B + (int64_t)l0 * es;  u.ldb = bd.ldb;
+        m.c = (void*)u.c;  m.ldc = bd.ldb;  m.b = u.c;  m.ldb = bd.ldb;
+        m.a = invb;  m.lda = p.IB;  m.m = ib;  m.n = bd.n;  m.k = ib;
+    }
+    p.upd[idx] = u;
+    p.mul[idx] = m;
+}
+
+template <typename T>
+static size_t trsm_scratch_bytes(int na, int64_t count)
+{
+    constexpr int IB = PanelCfg<T>::IB;
+    const int nblk = (na + IB - 1) / IB;
+    size_t inv = (size_t)nblk * IB * IB * sizeof(T);
+    size_t descs = 2 * (size_t)nblk * (size_t)count * sizeof(te_tile_desc);
+    return inv + descs + 256;
+}
+
+template <typename T>
+static int trsm_batched(int device, cudaStream_t stream, int dtype, int side, int uplo, int opa,
+                        int diag, const void* alpha, const T* A, int lda, int na,
+                        const te_trsm_desc* b_desc, int64_t count, int max_m, int max_n,
+                        void* scratch, size_t scratch_bytes)
+{
+    constexpr int IB = PanelCfg<T>::IB;
+    if (scratch_bytes < trsm_scratch_bytes<T>(na, count)) return TE_ERR_ARG;
+    int st = configure_panel_kernel<T>(device);
+    if (st != TE_OK) return st;
+    const int nblk = (na + IB - 1) / IB;
+    T* inv = (T*)scratch;
+    size_t off = ((size_t)nblk * IB * IB * sizeof(T) + 255) & ~(size_t)255;
+    te_tile_desc* upd = (te_tile_desc*)((char*)scratch + off);
+    te_tile_desc* mul = upd + (size_t)nblk * count;
+
+    // 1. inverses of the diagonal blocks (one CTA each); info is unused in this mode
+    potf2_trtri_kernel<T, IB><<<nblk, PANEL_THREADS, panel_smem_bytes<T>(), stream>>>(
+        const_cast<T*>(A), lda, uplo == TE_UPLO_UPPER, inv, nullptr, 0, 0,
+        diag == TE_DIAG_UNIT, (int64_t)IB + (int64_t)IB * lda, (int64_t)IB * IB, na);
+    TE_CUDA_CHECK(cudaGetLastError());
+
+    // 2. descriptors of every step
+    TrsmPlan p;
+    p.b = b_desc; p.upd = upd; p.mul = mul; p.A = A; p.inv = inv; p.count = count;
+    p.lda = lda; p.na = na; p.nblk = nblk; p.IB = IB; p.esize = (int)sizeof(T);
+    p.right = (side == TE_SIDE_RIGHT);
+    p.op_is_n = (opa == TE_OP_N);
+    p.eff_lower = ((uplo == TE_UPLO_LOWER) == (opa == TE_OP_N));
+    const int64_t total = (int64_t)nblk * count;
+    trsm_build_descs_kernel<<<(unsigned)((total + 127) / 128), 128, 0, stream>>>(p);
+    TE_CUDA_CHECK(cudaGetLastError());
+
+    // 3. block substitution, two GEMM launches per diagonal block
+    const double one[2] = {1.0, 0.0}, zero[2] = {0.0, 0.0}, mone[2] = {-1.0, 0.0};
+    for (int s = 0; s < nblk; ++s) {
+        const bool ascending = p.right ? !p.eff_lower : p.eff_lower;
+        const int blk = ascending ? s : (nblk - 1 - s);
+        const int ib = (na - blk * IB < IB) ? na - blk * IB : IB;
+        const int mm = p.right ? max_m : ib;
+        const int nn = p.right ? ib : max_n;
+        if (s > 0) {
+            // right: (X, op(A) block);  left: (op(A) block, X)
+            st = gemm_batched_any(device, stream, dtype, p.right ? TE_OP_N : opa,
+                                  p.right ? opa : TE_OP_N, mone, alpha,
+                                  upd + (size_t)s * count, count, mm, nn);
+            if (st != TE_OK) return st;
+        }
+        st = gemm_batched_any(device, stream, dtype, p.right ? TE_OP_N : opa,
+                              p.right ? opa : TE_OP_N, (s == 0) ? alpha : (const void*)one, zero,
+                              mul + (size_t)s * count, count, mm, nn);
+        if (st != TE_OK) return st;
+    }
+    return TE_OK;
+}
+
+}  // namespace te
+
+// ------------------------------------ C ABI ------------------------------------
+extern "C" size_t te_potrf_scratch_bytes(int dtype)
+{
+    return dtype == TE_C64 ? sizeof(te::zd) * 64 * 64 : sizeof(double) * 128 * 128;
+}
+
+extern "C" int te_potrf_tile(int device, void* stream, int dtype, int uplo, int n, void* A,
+                             int lda, int* info_dev, void* scratch, size_t scratch_bytes)
+{
+    if (!A || !info_dev || !scratch || n < 0 || lda < (n > 1 ? n : 1) ||
+        (uplo != TE_UPLO_LOWER && uplo != TE_UPLO_UPPER) ||
+        scratch_bytes < te_potrf_scratch_bytes(dtype))
+        return TE_ERR_ARG;
+    int st = te::set_device(device);
+    if (st != TE_OK) return st;
+    if (dtype == TE_F64)
+        return te::potrf_tile<double>(device, (cudaStream_t)stream, dtype, uplo, n, (double*)A, lda,
+                                      info_dev, (double*)scratch);
+    if (dtype == TE_C64)
+        return te::potrf_tile<te::zd>(device, (cudaStream_t)stream, dtype, uplo, n, (te::zd*)A,
+                                      lda, info_dev, (te::zd*)scratch);
+    return TE_ERR_ARG;
+}
+
+extern "C" size_t te_trsm_scratch_bytes(int dtype, int na, int64_t count)
+{
+    return dtype == TE_C64 ? te::trsm_scratch_bytes<te::zd>(na, count)
+                           : te::trsm_scratch_bytes<double>(na, count);
+}
+
+extern "C" int te_trsm_batched(int device, void* stream, int dtype, int side, int uplo, int opa,
+                               int diag, const void* alpha, const void* A, int lda, int na,
+                               const te_trsm_desc* b_desc, int64_t count, int32_t max_m,
+                               int32_t max_n, void* scratch, size_t scratch_bytes)
+{
+    if (!alpha || !A || na < 0 || count < 0 || (count > 0 && !b_desc) || !scratch ||
+        (side != TE_SIDE_LEFT && side != TE_SIDE_RIGHT) ||
+        (uplo != TE_UPLO_LOWER && uplo != TE_UPLO_UPPER) ||
+        (opa != TE_OP_N && opa != TE_OP_T && opa != TE_OP_C) ||
+        (diag != TE_DIAG_NONUNIT && diag != TE_DIAG_UNIT))
+        return TE_ERR_ARG;
+    if (count == 0 || na == 0 || max_m == 0 || max_n == 0)
+        return TE_OK;
+    int st = te::set_device(device);
+    if (st != TE_OK) return st;
+    if (dtype == TE_F64)
+        return te::trsm_batched<double>(device, (cudaStream_t)stream, dtype, side, uplo, opa, diag,
+                                        alpha, (const double*)A, lda, na, b_desc, count, max_m,
+                                        max_n, scratch, scratch_bytes);
+    if (dtype == TE_C64)
+        return te::trsm_batched<te::zd>(device, (cudaStream_t)stream, dtype, side, uplo, opa, diag,
+                                        alpha, (const te::zd*)A, lda, na, b_desc, count, max_m,
+                                        max_n, scratch, scratch_bytes);
+    return TE_ERR_ARG;
+}

@@ -1,0 +1,290 @@
+"""Parity of the CUDA kernels, called through the C ABI (include/tile_engine.h),
+against the CPU oracle on the same seeded (matgen) inputs.  Needs a GPU.
+
+Tolerances follow the reference's own tests: 3*sqrt(k)*eps elementwise for one block
+update (unit_test/test_internal_blas.cc:446-447), 50*eps*n-style bounds for the
+factorisation / solve (test/test_posv.cc:302-343 uses tol = 50).  Complex uses 4k
+real products per entry.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+
+pytestmark = pytest.mark.gpu
+EPS = np.finfo(np.float64).eps
+
+
+@pytest.fixture(scope="module")
+def te():
+    import torch
+    from slate_d35_b200 import lib
+    assert torch.cuda.is_available()
+    torch.cuda.set_device(0)
+    L = lib()
+    assert L.te_device_count() >= 1
+    return L
+
+
+def dev(a):
+    """numpy (F-order) -> torch cuda tensor holding the same bytes (col-major)."""
+    import torch
+    flat = np.ascontiguousarray(a.T).reshape(-1)           # column-major order
+    if np.iscomplexobj(a):
+        flat = flat.view(np.float64)
+    return torch.from_numpy(flat.copy()).cuda()
+
+
+def host(t, shape, dtype):
+    flat = t.cpu().numpy()
+    if dtype == np.complex128:
+        flat = flat.view(np.complex128)
+    m, n = shape
+    return np.asfortranarray(flat.reshape(n, m).T)
+
+
+def stream():
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+def scalar(x, dtype):
+    if dtype == np.complex128:
+        return (C.c_double * 2)(complex(x).real, complex(x).imag)
+    return (C.c_double * 1)(float(x))
+
+
+DT = {np.float64: 0, np.complex128: 1}
+
+
+def run_gemm(te, dtype, opa, opb, m, n, k, alpha, beta, flags=0, count=2, inline=False, ld_pad=0):
+    import torch
+    from slate_d35_b200 import TileDesc, check
+    descs = (TileDesc * count)()
+    keep, cases = [], []
+    for t in range(count):
+        ash = (m, k) if opa == "N" else (k, m)
+        bsh = (k, n) if opb == "N" else (n, k)
+        bufs = []
+        for seed, sh in ((10 + t, ash), (20 + t, bsh), (30 + t, (m, n))):
+            full = ol.matgen(seed, sh[0] + ld_pad, sh[1], dtype, dist=2)
+            bufs.append(full)
+        A, B, Cm = (b[: sh[0], :] for b, sh in zip(bufs, (ash, bsh, (m, n))))
+        dA, dB, dC = dev(bufs[0]), dev(bufs[1]), dev(bufs[2])
+        keep += [dA, dB, dC]
+        d = descs[t]
+        d.a, d.b, d.c = dA.data_ptr(), dB.data_ptr(), dC.data_ptr()
+        d.m, d.n, d.k = m, n, k
+        d.lda, d.ldb, d.ldc = bufs[0].shape[0], bufs[1].shape[0], bufs[2].shape[0]
+        d.flags = flags
+        cases.append((A, B, bufs[2], dC))
+    al, be = scalar(alpha, dtype), scalar(beta, dtype)
+    if inline:
+        check(te.te_gemm_inline(0, stream(), DT[dtype], ord(opa), ord(opb), al, be, descs, count))
+    else:
+        dd = torch.frombuffer(bytearray(bytes(descs)), dtype=torch.uint8).cuda()
+        check(te.te_gemm_batched(0, stream(), DT[dtype], ord(opa), ord(opb), al, be,
+                                 dd.data_ptr(), count, m, n))
+    torch.cuda.synchronize()
+    O = ol.oracle()
+    for A, B, Cfull, dC in cases:
+        want = Cfull.copy(order="F")
+        got = host(dC, Cfull.shape, dtype)
+        lda, ldb, ldc = A.base.shape[0] if A.base is not None else A.shape[0], \
+            B.base.shape[0] if B.base is not None else B.shape[0], Cfull.shape[0]
+        if dtype == np.float64:
+            O.oracle_tile_dgemm(ord(opa), ord(opb), m, n, k, float(alpha), ol.P(np.asfortranarray(A)),
+                                A.shape[0], ol.P(np.asfortranarray(B)), B.shape[0], float(beta),
+                                ol.P(want), ldc)
+        else:
+            O.oracle_tile_zgemm(ord(opa), ord(opb), m, n, k, ol.Z(alpha), ol.P(np.asfortranarray(A)),
+                                A.shape[0], ol.P(np.asfortranarray(B)), B.shape[0], ol.Z(beta),
+                                ol.P(want), ldc)
+        if flags & 1:
+            want = np.where(np.tril(np.ones_like(want, dtype=bool)), want, Cfull)
+        if flags & 2:
+            want = np.where(np.triu(np.ones_like(want, dtype=bool)), want, Cfull)
+        if (flags & 4) and dtype == np.complex128:
+            idx = np.arange(min(m, n))
+            want[idx, idx] = want[idx, idx].real
+        # padding rows (ld > m) must be untouched
+        assert np.array_equal(got[m:, :], Cfull[m:, :])
+        scale = max(1.0, np.abs(want[:m]).max())
+        kk = k * (4 if dtype == np.complex128 else 1)
+        err = np.abs(got[:m] - want[:m]).max() / scale
+        assert err <= 3 * np.sqrt(max(kk, 1)) * EPS * 2, (err, opa, opb, m, n, k)
+
+
+@pytest.mark.parametrize("opa", "NT")
+@pytest.mark.parametrize("opb", "NT")
+@pytest.mark.parametrize("shape", [(80, 64, 16), (512, 512, 512), (130, 257, 37), (1, 1, 1),
+                                   (128, 128, 0), (129, 127, 513)])
+def test_dgemm_tiles_vs_oracle(te, opa, opb, shape):
+    m, n, k = shape
+    run_gemm(te, np.float64, opa, opb, m, n, k, 3.141592653589793, 2.718281828459045)
+
+
+@pytest.mark.parametrize("inline", [False, True])
+@pytest.mark.parametrize("ld_pad", [0, 1, 2])
+def test_dgemm_ragged_ld_and_inline(te, inline, ld_pad):
+    """odd leading dimensions take the 8-byte copy path (fromLAPACK views with ld = m+1,
+    unit_test/test_internal_blas.cc:300-312)"""
+    run_gemm(te, np.float64, "N", "T", 80, 64, 16, -1.0, 1.0, inline=inline, ld_pad=ld_pad)
+    run_gemm(te, np.float64, "T", "N", 200, 131, 77, 0.5, 0.0, inline=inline, ld_pad=ld_pad)
+
+
+@pytest.mark.parametrize("flags", [1, 2])
+@pytest.mark.parametrize("beta", [0.0, 1.0])
+def test_dsyrk_diagonal_tile_mask(te, flags, beta):
+    run_gemm(te, np.float64, "N", "T", 300, 300, 64, -1.0, beta, flags=flags)
+
+
+def test_beta_zero_ignores_nan_in_c(te):
+    import torch
+    from slate_d35_b200 import TileDesc, check
+    m = n = k = 64
+    A, B = ol.matgen(1, m, k), ol.matgen(2, k, n)
+    dA, dB = dev(A), dev(B)
+    dC = torch.full((m * n,), float("nan"), dtype=torch.float64, device="cuda")
+    d = (TileDesc * 1)()
+    d[0].a, d[0].b, d[0].c = dA.data_ptr(), dB.data_ptr(), dC.data_ptr()
+    d[0].m, d[0].n, d[0].k, d[0].lda, d[0].ldb, d[0].ldc = m, n, k, m, k, m
+    check(te.te_gemm_inline(0, stream(), 0, ord("N"), ord("N"), scalar(1.0, np.float64),
+                            scalar(0.0, np.float64), d, 1))
+    got = host(dC, (m, n), np.float64)
+    assert np.abs(got - A @ B).max() <= 3 * np.sqrt(k) * EPS * np.abs(A @ B).max()
+
+
+@pytest.mark.parametrize("uplo", "LU")
+@pytest.mark.parametrize("n", [1, 37, 128, 200, 512])
+def test_dpotrf_tile_vs_oracle(te, uplo, n):
+    import torch
+    from slate_d35_b200 import check
+    lda = n + 3
+    full = ol.matgen(5, lda, n)
+    A = full[:n, :]
+    A[np.arange(n), np.arange(n)] += n
+    want = full.copy(order="F")
+    assert ol.oracle().oracle_tile_dpotrf(ord(uplo), n, ol.P(want), lda) == 0
+    dA = dev(full)
+    info = torch.full((1,), 7, dtype=torch.int32, device="cuda")
+    sb = te.te_potrf_scratch_bytes(0)
+    scratch = torch.empty(sb, dtype=torch.uint8, device="cuda")
+    check(te.te_potrf_tile(0, stream(), 0, ord(uplo), n, dA.data_ptr(), lda, info.data_ptr(),
+                           scratch.data_ptr(), sb))
+    got = host(dA, (lda, n), np.float64)
+    assert int(info.item()) == 0
+    # the other triangle and the padding rows are untouched; the factor matches
+    assert np.abs(got - want).max() / np.abs(want).max() <= 50 * EPS
+    tri = (lambda x: np.triu(x[:n], 1)) if uplo == "L" else (lambda x: np.tril(x[:n], -1))
+    assert np.array_equal(tri(got), tri(full))
+    assert np.array_equal(got[n:], full[n:])
+
+
+def test_dpotrf_tile_info(te):
+    import torch
+    from slate_d35_b200 import check
+    n = 300
+    A = ol.matgen(5, n, n)
+    A[np.arange(n), np.arange(n)] += n
+    A[170, 170] = -1.0
+    dA = dev(A)
+    info = torch.zeros(1, dtype=torch.int32, device="cuda")
+    sb = te.te_potrf_scratch_bytes(0)
+    scratch = torch.empty(sb, dtype=torch.uint8, device="cuda")
+    check(te.te_potrf_tile(0, stream(), 0, ord("L"), n, dA.data_ptr(), n, info.data_ptr(),
+                           scratch.data_ptr(), sb))
+    want = A.copy(order="F")
+    assert int(info.item()) == ol.oracle().oracle_tile_dpotrf(ord("L"), n, ol.P(want), n) == 171
+
+
+@pytest.mark.parametrize("side,uplo,op,diag", [
+    ("R", "L", "C", "N"),      # the potrf panel solve (src/potrf.cc:113-119)
+    ("R", "L", "N", "N"), ("R", "U", "N", "U"), ("R", "U", "T", "N"),
+    ("L", "L", "N", "N"), ("L", "L", "T", "U"), ("L", "U", "N", "N"), ("L", "U", "C", "N")])
+@pytest.mark.parametrize("na", [100, 512])
+def test_dtrsm_batched_vs_oracle(te, side, uplo, op, diag, na):
+    import torch
+    from slate_d35_b200 import TrsmDesc, check
+    count = 3
+    lda = na + 1
+    Afull = ol.matgen(16, lda, na, dist=2)
+    Afull[np.arange(na), np.arange(na)] += na ** 0.5 * 2
+    dA = dev(Afull)
+    descs = (TrsmDesc * count)()
+    keep, cases = [], []
+    sizes = [na, 70, 300]
+    for t in range(count):
+        m, n = (sizes[t], na) if side == "R" else (na, sizes[t])
+        B = ol.matgen(40 + t, m, n, dist=2)
+        dB = dev(B)
+        keep.append(dB)
+        descs[t].b, descs[t].m, descs[t].n, descs[t].ldb = dB.data_ptr(), m, n, m
+        cases.append((B, dB, m, n))
+    dd = torch.frombuffer(bytearray(bytes(descs)), dtype=torch.uint8).cuda()
+    sb = te.te_trsm_scratch_bytes(0, na, count)
+    scratch = torch.empty(sb, dtype=torch.uint8, device="cuda")
+    alpha = 0.75
+    check(te.te_trsm_batched(0, stream(), 0, ord(side), ord(uplo), ord(op), ord(diag),
+                             scalar(alpha, np.float64), dA.data_ptr(), lda, na, dd.data_ptr(), count,
+                             max(c[2] for c in cases), max(c[3] for c in cases),
+                             scratch.data_ptr(), sb))
+    torch.cuda.synchronize()
+    for B, dB, m, n in cases:
+        want = B.copy(order="F")
+        ol.oracle().oracle_tile_dtrsm(ord(side), ord(uplo), ord(op), ord(diag), m, n, alpha,
+                                      ol.P(Afull), lda, ol.P(want), m)
+        got = host(dB, (m, n), np.float64)
+        err = np.abs(got - want).max() / np.abs(want).max()
+        assert err <= 50 * EPS * np.sqrt(na), (err, side, uplo, op, diag)
+
+
+def test_matgen_device_bit_exact(te):
+    import torch
+    from slate_d35_b200 import check
+    for dtype in (np.float64, np.complex128):
+        m, n, ld = 77, 45, 80
+        buf = torch.zeros(ld * n * (2 if dtype == np.complex128 else 1), dtype=torch.float64,
+                          device="cuda")
+        check(te.te_matgen_tile(0, stream(), DT[dtype], 1, 12345, m, n, 98300, 65530,
+                                buf.data_ptr(), ld, 0.0))
+        got = host(buf, (ld, n), dtype)[:m]
+        assert np.array_equal(got, ol.matgen(12345, m, n, dtype, 1, 98300, 65530))
+    buf = torch.zeros(64 * 64, dtype=torch.float64, device="cuda")
+    check(te.te_matgen_tile(0, stream(), 0, 1, 3, 64, 64, 128, 128, buf.data_ptr(), 64, 1000.0))
+    want = ol.matgen(3, 64, 64, ioff=128, joff=128)
+    want[np.arange(64), np.arange(64)] += 1000.0
+    assert np.array_equal(host(buf, (64, 64), np.float64), want)
+
+
+def test_pool_semantics(te):
+    """unit_test/test_Memory.cc:58-96,147-211: reserve, pop, grow by one, push back, clear."""
+    from slate_d35_b200 import check
+    vp, sz = C.c_void_p, C.c_size_t
+    pool = vp()
+    check(te.te_pool_create(0, 8 * 100 * 100, C.byref(pool)))
+    av, cap, bb = sz(), sz(), sz()
+    check(te.te_pool_stats(pool, C.byref(av), C.byref(cap), C.byref(bb)))
+    assert (av.value, cap.value) == (0, 0) and bb.value >= 80000 and bb.value % 256 == 0
+    check(te.te_pool_reserve(pool, 4))
+    check(te.te_pool_stats(pool, C.byref(av), C.byref(cap), None))
+    assert (av.value, cap.value) == (4, 4)
+    blocks = []
+    for i in range(6):                                   # 2 more than reserved: grows one by one
+        b = vp()
+        check(te.te_pool_alloc(pool, C.byref(b)))
+        assert b.value and b.value % 256 == 0 and b.value not in blocks
+        blocks.append(b.value)
+        check(te.te_pool_stats(pool, C.byref(av), C.byref(cap), None))
+        assert cap.value == max(4, i + 1) and av.value == cap.value - (i + 1)
+    assert blocks[1] - blocks[0] == bb.value              # slab blocks are contiguous, ascending
+    for b in blocks:
+        check(te.te_pool_free(pool, b))
+    check(te.te_pool_stats(pool, C.byref(av), C.byref(cap), None))
+    assert (av.value, cap.value) == (6, 6)
+    check(te.te_pool_clear(pool))
+    check(te.te_pool_stats(pool, C.byref(av), C.byref(cap), None))
+    assert (av.value, cap.value) == (0, 0)
+    check(te.te_pool_destroy(pool))
