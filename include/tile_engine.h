@@ -71,6 +71,7 @@ int te_event_destroy(void* event);
 int te_event_record(void* event, void* stream);
 int te_stream_wait_event(void* stream, void* event);
 int te_event_sync(void* event);
+int te_event_query_done(void* event);   /* 1 finished, 0 not yet, -1 error */
 int te_event_elapsed_ms(void* start, void* stop, float* ms);
 
 int te_device_malloc(int device, size_t bytes, void** ptr);
@@ -201,6 +202,38 @@ int te_trsm_batched(int device, void* stream, int dtype, int side, int uplo, int
                     const void* alpha, const void* A, int lda, int na,
                     const te_trsm_desc* b_desc, int64_t count, int32_t max_m, int32_t max_n,
                     void* scratch, size_t scratch_bytes);
+
+/* ------------------------------------------------------------------------
+ * Tile broadcasts between the box's GPUs over NCCL (one rank per GPU).
+ *
+ * Replaces the MPI side of BaseMatrix::tileBcast / listBcast / listBcastMT:
+ *   tileBcastToSet / tileIbcastToSet   include/slate/BaseMatrix.hh:2283-2387
+ *   internal::cubeBcastPattern         src/internal/internal_comm.cc:72-115
+ *   Tile::isend / irecv                include/slate/Tile.hh:1084-1200
+ *   internal::reduce_info (MPI_MIN)    src/internal/internal_reduce_info.cc:31
+ * A broadcast of tile (i, j) to a set of ranks is: between te_comm_group_start
+ * and te_comm_group_end, the root calls te_comm_send once per destination and
+ * each destination calls te_comm_recv; every rank brackets the same list.
+ * Buffers are DEVICE memory; everything is enqueued on `stream`.
+ * te_comm_unique_id is called on one rank and its TE_COMM_ID_BYTES bytes are
+ * handed to the others by the launcher (torch.distributed, MPI, a file ...).
+ * ---------------------------------------------------------------------- */
+#define TE_COMM_ID_BYTES 128
+enum { TE_REDUCE_SUM = 0, TE_REDUCE_MIN = 1, TE_REDUCE_MAX = 2 };
+typedef struct te_comm te_comm;
+int te_comm_unique_id(void* id_out, size_t bytes);
+int te_comm_init_rank(const void* id, size_t bytes, int nranks, int rank, int device,
+                      te_comm** comm);
+int te_comm_destroy(te_comm* comm);
+int te_comm_rank(const te_comm* comm);
+int te_comm_size(const te_comm* comm);
+int te_comm_group_start(void);
+int te_comm_group_end(void);
+int te_comm_send(te_comm* comm, const void* buf, size_t bytes, int peer, void* stream);
+int te_comm_recv(te_comm* comm, void* buf, size_t bytes, int peer, void* stream);
+int te_comm_bcast(te_comm* comm, void* buf, size_t bytes, int root, void* stream);
+int te_comm_allreduce_i64(te_comm* comm, int64_t* buf_dev, size_t count, int op, void* stream);
+int te_comm_allreduce_f64(te_comm* comm, double* buf_dev, size_t count, int op, void* stream);
 
 /* ------------------------------------------------------------------------
  * Harness kernels around the hot path (inputs and residual checks).

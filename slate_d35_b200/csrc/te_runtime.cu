@@ -275,3 +275,13 @@ extern "C" int te_pool_destroy(te_pool* p)
     delete p;
     return st;
 }
+
+// 1 = everything recorded in the event has finished, 0 = not yet, -1 = error
+extern "C" int te_event_query_done(void* event)
+{
+    cudaError_t e = cudaEventQuery((cudaEvent_t)event);
+    if (e == cudaSuccess) return 1;
+    if (e == cudaErrorNotReady) return 0;
+    te::set_last_error("cudaEventQuery", cudaGetErrorString(e));
+    return -1;
+}

@@ -1,0 +1,252 @@
+"""Python face of libslate_b200.so, the host C++ mirror of SLATE's interface
+(slate::Matrix / HermitianMatrix, slate::gemm, slate::potrf, internal::* on
+Target::Devices).  Used by the tests, bench.py and smoke(); the product is the
+C++/CUDA underneath, this file only marshals arguments.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from ._lib import lib as _te_lib
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+HOST_LIB_PATH = os.path.join(_HERE, "lib", "libslate_b200.so")
+
+F64, C64 = 0, 1
+GENERAL, HERMITIAN, SYMMETRIC, TRIANGULAR = 0, 1, 2, 3
+TARGET_DEVICES, TARGET_HOSTTASK = ord("D"), ord("T")
+
+_lib = None
+i64, vp, dp = C.c_int64, C.c_void_p, C.POINTER(C.c_double)
+
+
+def hostlib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    _te_lib()     # loads libtile_engine.so first (and fails loudly if it is missing)
+    if not os.path.exists(HOST_LIB_PATH):
+        raise RuntimeError(f"{HOST_LIB_PATH} is missing: run __graft_entry__.build()")
+    L = C.CDLL(HOST_LIB_PATH)
+    L.sb_last_error.restype = C.c_char_p
+    L.sb_initialize.argtypes = [C.c_int, C.c_int, C.c_int, vp]
+    L.sb_matrix_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, i64, i64, i64, C.c_int,
+                                   C.c_int, C.c_int, vp, i64, C.POINTER(vp)]
+    L.sb_matrix_destroy.argtypes = [vp]
+    L.sb_matrix_generate.argtypes = [vp, i64, C.c_int, C.c_int]
+    L.sb_matrix_to_host.argtypes = [vp, vp, i64]
+    L.sb_matrix_from_host.argtypes = [vp, vp, i64]
+    L.sb_matrix_sumsq.argtypes = [vp, dp]
+    L.sb_pool_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(i64)]
+    L.sb_gemm.argtypes = [C.c_int, C.c_int, dp, vp, vp, dp, vp, C.c_int, C.c_int,
+                          C.POINTER(C.c_float)]
+    L.sb_potrf.argtypes = [vp, C.c_int, C.c_int, C.POINTER(i64), C.POINTER(C.c_float)]
+    L.sb_potrf_residual.argtypes = [vp, i64, C.c_int, dp, dp]
+    L.sb_internal_gemm.argtypes = [C.c_int, C.c_int, C.c_int, dp, vp, vp, dp, vp, C.c_int, C.c_int]
+    L.sb_internal_herk.argtypes = [C.c_int, C.c_int, C.c_double, vp, C.c_double, vp, C.c_int]
+    L.sb_internal_syrk.argtypes = [C.c_int, C.c_int, dp, vp, dp, vp, C.c_int]
+    L.sb_internal_trsm.argtypes = [C.c_int, C.c_int, C.c_int, dp, vp, vp, C.c_int]
+    L.sb_internal_potrf.argtypes = [vp, C.c_int, C.POINTER(i64)]
+    _lib = L
+    return L
+
+
+class SlateError(RuntimeError):
+    pass
+
+
+def _check(status):
+    if status != 0:
+        raise SlateError(hostlib().sb_last_error().decode())
+
+
+def _scalar(x):
+    z = complex(x)
+    return (C.c_double * 2)(z.real, z.imag)
+
+
+_initialized = False
+
+
+def initialize(device=None, rank=0, size=1, nccl_id=None):
+    """Bind this process to a GPU (default $LOCAL_RANK) and, for size > 1, join the NCCL
+    communicator whose unique id rank 0 created with nccl_unique_id()."""
+    global _initialized
+    if device is None:
+        device = int(os.environ.get("LOCAL_RANK", "0"))
+    buf = None
+    if size > 1:
+        assert nccl_id is not None and len(nccl_id) == 128
+        buf = C.create_string_buffer(bytes(nccl_id), 128)
+    _check(hostlib().sb_initialize(device, rank, size, buf))
+    _initialized = True
+
+
+def finalize():
+    global _initialized
+    if _initialized:
+        _check(hostlib().sb_finalize())
+    _initialized = False
+
+
+def nccl_unique_id():
+    buf = C.create_string_buffer(128)
+    st = _te_lib().te_comm_unique_id(buf, 128)
+    if st != 0:
+        raise SlateError(_te_lib().te_last_error().decode())
+    return buf.raw
+
+
+def sync():
+    _check(hostlib().sb_sync())
+
+
+def _dtype_code(dtype):
+    return C64 if np.dtype(dtype) == np.complex128 else F64
+
+
+class _Base:
+    kind = GENERAL
+
+    def __init__(self, m, n, nb, p=1, q=1, dtype=np.float64, origin="D", uplo="L", diag="N",
+                 host_array=None):
+        """host_array: column-major (ld x n) buffer whose first m rows are the matrix."""
+        if not _initialized:
+            initialize()
+        self.m, self.n, self.nb, self.p, self.q = m, n, nb, p, q
+        self.dtype = np.dtype(dtype)
+        self.uplo = uplo
+        self._host_array = host_array          # keep user memory alive (fromLAPACK)
+        h = vp()
+        ptr, ld = None, 0
+        if host_array is not None:
+            assert host_array.flags.f_contiguous and host_array.dtype == self.dtype
+            assert host_array.shape[0] >= m and host_array.shape[1] == n
+            ptr, ld = host_array.ctypes.data, host_array.shape[0]
+        _check(hostlib().sb_matrix_create(_dtype_code(dtype), self.kind, ord(uplo), ord(diag), m, n,
+                                          nb, p, q, ord(origin), ptr, ld, C.byref(h)))
+        self.h = h
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None):
+                hostlib().sb_matrix_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def free(self):
+        if self.h:
+            _check(hostlib().sb_matrix_destroy(self.h))
+            self.h = None
+
+    def generate(self, seed, dominant=False, dist=1):
+        """matgen 'rand' (dist 1) / 'rands' (dist 2); dominant adds n to the diagonal."""
+        _check(hostlib().sb_matrix_generate(self.h, seed, int(dominant), dist))
+        return self
+
+    def to_numpy(self):
+        """Gather this rank's tiles into a full-size column-major array (zeros elsewhere)."""
+        out = np.zeros((self.m, self.n), dtype=self.dtype, order="F")
+        _check(hostlib().sb_matrix_to_host(self.h, out.ctypes.data, max(self.m, 1)))
+        return out
+
+    def from_numpy(self, a):
+        a = np.asfortranarray(a, dtype=self.dtype)
+        assert a.shape == (self.m, self.n)
+        _check(hostlib().sb_matrix_from_host(self.h, a.ctypes.data, max(self.m, 1)))
+        return self
+
+    def sumsq(self):
+        out = C.c_double()
+        _check(hostlib().sb_matrix_sumsq(self.h, C.byref(out)))
+        return out.value
+
+    def pool_stats(self):
+        a, c = i64(), i64()
+        _check(hostlib().sb_pool_stats(self.h, C.byref(a), C.byref(c)))
+        return a.value, c.value
+
+
+class Matrix(_Base):
+    kind = GENERAL
+
+    @classmethod
+    def fromLAPACK(cls, a, nb, p=1, q=1, m=None):
+        """View of the first m rows (default all) of the column-major array a (ld = a.shape[0])."""
+        return cls(a.shape[0] if m is None else m, a.shape[1], nb, p, q, a.dtype, origin="H",
+                   host_array=a)
+
+
+class HermitianMatrix(_Base):
+    kind = HERMITIAN
+
+    def __init__(self, uplo, n, nb, p=1, q=1, dtype=np.float64, origin="D", host_array=None):
+        super().__init__(n, n, nb, p, q, dtype, origin, uplo=uplo, host_array=host_array)
+
+    @classmethod
+    def fromLAPACK(cls, uplo, a, nb, p=1, q=1):
+        return cls(uplo, a.shape[0], nb, p, q, a.dtype, origin="H", host_array=a)
+
+
+class SymmetricMatrix(HermitianMatrix):
+    kind = SYMMETRIC
+
+
+class TriangularMatrix(_Base):
+    kind = TRIANGULAR
+
+    def __init__(self, uplo, diag, n, nb, p=1, q=1, dtype=np.float64, origin="D", host_array=None):
+        super().__init__(n, n, nb, p, q, dtype, origin, uplo=uplo, diag=diag, host_array=host_array)
+
+    @classmethod
+    def fromLAPACK(cls, uplo, diag, a, nb, p=1, q=1):
+        return cls(uplo, diag, a.shape[0], nb, p, q, a.dtype, origin="H", host_array=a)
+
+
+def gemm(alpha, A, B, beta, Cm, opa="N", opb="N", lookahead=1, target="D", timed=False):
+    """slate::gemm: C = alpha op(A) op(B) + beta C.  Returns device milliseconds if timed."""
+    ms = C.c_float()
+    _check(hostlib().sb_gemm(ord(opa), ord(opb), _scalar(alpha), A.h, B.h, _scalar(beta), Cm.h,
+                             lookahead, ord(target), C.byref(ms) if timed else None))
+    return ms.value if timed else None
+
+
+def potrf(A, lookahead=1, target="D", timed=False):
+    """slate::potrf.  Returns info, or (info, device milliseconds) if timed."""
+    info, ms = i64(), C.c_float()
+    _check(hostlib().sb_potrf(A.h, lookahead, ord(target), C.byref(info),
+                              C.byref(ms) if timed else None))
+    return (info.value, ms.value) if timed else info.value
+
+
+def potrf_residual(A, seed, dominant=True):
+    """(||A0 - L L^H||_F^2, ||A0||_F^2) over this rank's tiles; A holds the lower factor."""
+    r, a0 = C.c_double(), C.c_double()
+    _check(hostlib().sb_potrf_residual(A.h, seed, int(dominant), C.byref(r), C.byref(a0)))
+    return r.value, a0.value
+
+
+def internal_gemm(alpha, A, B, beta, Cm, opa="N", opb="N", opc="N", target="D", queue=0):
+    _check(hostlib().sb_internal_gemm(ord(opa), ord(opb), ord(opc), _scalar(alpha), A.h, B.h,
+                                      _scalar(beta), Cm.h, ord(target), queue))
+
+
+def internal_herk(alpha, A, beta, Cm, opa="N", opc="N", queue=0):
+    _check(hostlib().sb_internal_herk(ord(opa), ord(opc), float(alpha), A.h, float(beta), Cm.h, queue))
+
+
+def internal_syrk(alpha, A, beta, Cm, opa="N", opc="N", queue=0):
+    _check(hostlib().sb_internal_syrk(ord(opa), ord(opc), _scalar(alpha), A.h, _scalar(beta), Cm.h,
+                                      queue))
+
+
+def internal_trsm(side, alpha, A, B, opa="N", opb="N", queue=0):
+    _check(hostlib().sb_internal_trsm(ord(side), ord(opa), ord(opb), _scalar(alpha), A.h, B.h, queue))
+
+
+def internal_potrf(A, queue=0):
+    info = i64()
+    _check(hostlib().sb_internal_potrf(A.h, queue, C.byref(info)))
+    return info.value

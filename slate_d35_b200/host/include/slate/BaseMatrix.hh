@@ -1,0 +1,564 @@
+// slate/BaseMatrix.hh -- distributed tiled matrix views over a 2D block-cyclic p x q
+// grid: sub / transpose views, tile access, MOSI coherence between the host and the
+// device instance of a tile, tile broadcasts, workspace release.
+//
+// Mirrors the parts of include/slate/BaseMatrix.hh that slate::gemm and slate::potrf
+// touch (reference lines cited per method).  Deliberate differences:
+//   * one rank drives one GPU; broadcasts go GPU to GPU over NCCL
+//     (tile_engine.h te_comm_*), never through host staging or MPI;
+//   * nothing here blocks the host except copies TO the host: device-side ordering is
+//     by events (Engine), and erased workspace blocks return to the pool deferred.
+// Methods that take a compute `queue` extend the reference signature with a trailing
+// defaulted argument; -1 means "no device consumer yet".
+#ifndef SLATE_B200_BASE_MATRIX_HH
+#define SLATE_B200_BASE_MATRIX_HH
+
+#include "slate/MatrixStorage.hh"
+
+#include <algorithm>
+#include <list>
+#include <set>
+#include <vector>
+
+namespace slate {
+
+template <typename scalar_t> class BaseMatrix;
+template <typename scalar_t> class Matrix;
+
+template <typename scalar_t>
+class BaseMatrix {
+public:
+    using ij_tuple = slate::ij_tuple;
+    /// include/slate/BaseMatrix.hh:42-50
+    using BcastList =
+        std::vector<std::tuple<int64_t, int64_t, std::list<BaseMatrix<scalar_t>>>>;
+    using BcastListTag =
+        std::vector<std::tuple<int64_t, int64_t, std::list<BaseMatrix<scalar_t>>, int64_t>>;
+    static constexpr bool is_complex = slate::is_complex<scalar_t>::value;
+    static constexpr bool is_real = !is_complex;
+
+    BaseMatrix()
+        : ioffset_(0), joffset_(0), mt_(0), nt_(0), uplo_(Uplo::General), op_(Op::NoTrans),
+          layout_(Layout::ColMajor), origin_(Target::Host)
+    {}
+
+protected:
+    BaseMatrix(int64_t m, int64_t n, int64_t mb, int64_t nb, GridOrder order, int p, int q,
+               MPI_Comm comm)
+        : ioffset_(0), joffset_(0), uplo_(Uplo::General), op_(Op::NoTrans),
+          layout_(Layout::ColMajor), origin_(Target::Host),
+          storage_(std::make_shared<MatrixStorage<scalar_t>>(m, n, mb, nb, order, p, q, comm))
+    {
+        mt_ = storage_->mt_;
+        nt_ = storage_->nt_;
+    }
+
+    /// sub-matrix view of tiles [i1..i2] x [j1..j2] (include/slate/BaseMatrix.hh:863-905)
+    BaseMatrix(BaseMatrix const& orig, int64_t i1, int64_t i2, int64_t j1, int64_t j2)
+        : BaseMatrix(orig)
+    {
+        if (i2 < i1 || j2 < j1) {       // empty view
+            mt_ = nt_ = 0;
+            return;
+        }
+        slate_assert(0 <= i1 && i2 < orig.mt() && 0 <= j1 && j2 < orig.nt());
+        if (op_ == Op::NoTrans) {
+            ioffset_ += i1;  joffset_ += j1;
+            mt_ = i2 - i1 + 1;  nt_ = j2 - j1 + 1;
+        }
+        else {
+            ioffset_ += j1;  joffset_ += i1;
+            mt_ = j2 - j1 + 1;  nt_ = i2 - i1 + 1;
+        }
+    }
+
+public:
+    // ---- shape -------------------------------------------------------------------------
+    int64_t mt() const { return op_ == Op::NoTrans ? mt_ : nt_; }
+    int64_t nt() const { return op_ == Op::NoTrans ? nt_ : mt_; }
+    Op op() const { return op_; }
+    Uplo uplo() const { return uploLogical(); }
+    Uplo uploLogical() const
+    {
+        if (uplo_ == Uplo::General) return Uplo::General;
+        if ((uplo_ == Uplo::Lower) == (op_ == Op::NoTrans)) return Uplo::Lower;
+        return Uplo::Upper;
+    }
+    Uplo uploPhysical() const { return uplo_; }
+    Layout layout() const { return layout_; }
+    Target origin() const { return origin_; }
+
+    int64_t tileMb(int64_t i) const
+    {
+        return op_ == Op::NoTrans ? storage_->tileMb(ioffset_ + i) : storage_->tileNb(joffset_ + i);
+    }
+    int64_t tileNb(int64_t j) const
+    {
+        return op_ == Op::NoTrans ? storage_->tileNb(joffset_ + j) : storage_->tileMb(ioffset_ + j);
+    }
+    int64_t m() const { int64_t s = 0; for (int64_t i = 0; i < mt(); ++i) s += tileMb(i); return s; }
+    int64_t n() const { int64_t s = 0; for (int64_t j = 0; j < nt(); ++j) s += tileNb(j); return s; }
+
+    /// (i, j) of the view -> global storage index (BaseMatrix.hh:3975-3990)
+    ij_tuple globalIndex(int64_t i, int64_t j) const
+    {
+        return op_ == Op::NoTrans ? ij_tuple{ioffset_ + i, joffset_ + j}
+                                  : ij_tuple{ioffset_ + j, joffset_ + i};
+    }
+
+    int tileRank(int64_t i, int64_t j) const { return storage_->tileRank(globalIndex(i, j)); }
+    int tileDevice(int64_t i, int64_t j) const { return storage_->tileDevice(globalIndex(i, j)); }
+    bool tileIsLocal(int64_t i, int64_t j) const { return storage_->tileIsLocal(globalIndex(i, j)); }
+    bool tileExists(int64_t i, int64_t j, int device = AnyDevice) const
+    {
+        auto* node = storage_->find(globalIndex(i, j));
+        if (!node) return false;
+        if (device == AnyDevice) return true;
+        return device == HostNum ? node->host != nullptr : node->dev != nullptr;
+    }
+    int num_devices() const { return Engine::instance().num_devices(); }
+    MPI_Comm mpiComm() const { return storage_->comm_; }
+    int mpiRank() const { return storage_->comm_->rank; }
+    void gridinfo(GridOrder* order, int* p, int* q, int* myrow, int* mycol) const
+    {
+        *order = storage_->order_;  *p = storage_->p_;  *q = storage_->q_;
+        int r = storage_->comm_->rank;
+        if (storage_->order_ == GridOrder::Col) { *myrow = r % *p;  *mycol = r / *p; }
+        else { *myrow = r / *q;  *mycol = r % *q; }
+    }
+    void* compute_queue(int device, int queue_index) { return Engine::instance().compute_stream(queue_index); }
+    void* comm_queue(int device) { return Engine::instance().comm_stream(); }
+
+    /// Tile handle with this view's op / uplo applied (BaseMatrix.hh:1066-1090).
+    Tile<scalar_t> operator()(int64_t i, int64_t j, int device = HostNum)
+    {
+        auto& node = storage_->at(globalIndex(i, j));
+        Tile<scalar_t>* t = (device == HostNum) ? node.host : node.dev;
+        if (!t)
+            slate_error("tile (" + std::to_string(i) + ", " + std::to_string(j) + ") has no instance on "
+                        + (device == HostNum ? std::string("the host") : std::string("the device")));
+        Tile<scalar_t> tile = *t;
+        tile.op(op_);
+        if (i == j) tile.uplo(uplo_);
+        return tile;
+    }
+
+    // ---- tile management -----------------------------------------------------------------
+    /// workspace tile (BaseMatrix.hh:1253-1270)
+    Tile<scalar_t>* tileInsertWorkspace(int64_t i, int64_t j, int device)
+    {
+        return storage_->tileInsert(globalIndex(i, j), device, TileKind::Workspace);
+    }
+    Tile<scalar_t>* tileInsert(int64_t i, int64_t j, int device = HostNum)
+    {
+        auto* t = storage_->tileInsert(globalIndex(i, j), device, TileKind::SlateOwned);
+        auto& node = storage_->at(globalIndex(i, j));
+        (device == HostNum ? node.host_state : node.dev_state) = MOSI::Shared;
+        return t;
+    }
+    Tile<scalar_t>* tileInsert(int64_t i, int64_t j, int device, scalar_t* A, int64_t ld)
+    {
+        return storage_->tileInsert(globalIndex(i, j), device, A, ld);
+    }
+    void tileErase(int64_t i, int64_t j, int device)
+    {
+        storage_->tileErase(globalIndex(i, j), device);
+    }
+
+    /// MOSI state of one instance (BaseMatrix.hh:1719-1740)
+    short tileState(int64_t i, int64_t j, int device = HostNum)
+    {
+        auto& node = storage_->at(globalIndex(i, j));
+        return device == HostNum ? node.host_state : node.dev_state;
+    }
+
+    /// Marks the instance on `device` Modified and the other Invalid (BaseMatrix.hh:2811-2840).
+    void tileModified(int64_t i, int64_t j, int device = HostNum, int queue = -1)
+    {
+        auto& node = storage_->at(globalIndex(i, j));
+        if (device == HostNum) {
+            slate_assert(node.host);
+            node.host_state = MOSI::Modified;
+            if (node.dev) node.dev_state = MOSI::Invalid;
+        }
+        else {
+            slate_assert(node.dev);
+            node.dev_state = MOSI::Modified;
+            if (node.host) node.host_state = MOSI::Invalid;
+            if (queue >= 0) node.write_queue = queue;
+        }
+    }
+
+    /// Makes the instance on `device` valid, copying from the other one if needed
+    /// (tileGet, BaseMatrix.hh:2640-2720).  Host-to-device copies are enqueued on the comm
+    /// stream (call Engine::mark_comm + queue_wait_comm before the consuming launch, or use
+    /// the set overloads which do it); device-to-host copies wait for the producing queue
+    /// and are complete on return.
+    void tileGetForReading(int64_t i, int64_t j, int device = HostNum,
+                           LayoutConvert = LayoutConvert::None, int queue = -1)
+    {
+        tileGet(i, j, device, false, queue);
+        if (device == HostNum) finishHostCopies();
+    }
+    void tileGetForWriting(int64_t i, int64_t j, int device = HostNum,
+                           LayoutConvert = LayoutConvert::None, int queue = -1)
+    {
+        tileGet(i, j, device, true, queue);
+        if (device == HostNum) finishHostCopies();
+    }
+    void tileGetForReading(std::set<ij_tuple>& tiles, int device,
+                           LayoutConvert = LayoutConvert::None, int queue = -1)
+    {
+        for (auto const& ij : tiles) tileGet(std::get<0>(ij), std::get<1>(ij), device, false, queue);
+        finishSet(device, queue);
+    }
+    void tileGetForWriting(std::set<ij_tuple>& tiles, int device,
+                           LayoutConvert = LayoutConvert::None, int queue = -1)
+    {
+        for (auto const& ij : tiles) tileGet(std::get<0>(ij), std::get<1>(ij), device, true, queue);
+        finishSet(device, queue);
+    }
+    /// BaseMatrix.hh:3081-3104 (fetch_C in gemmC.cc:70-74)
+    void tileGetAllForWritingOnDevices(LayoutConvert = LayoutConvert::None, int queue = -1)
+    {
+        for (int64_t j = 0; j < nt(); ++j)
+            for (int64_t i = 0; i < mt(); ++i)
+                if (tileIsLocal(i, j) && inStoredTriangle(i, j)) tileGet(i, j, 0, true, queue);
+        finishSet(0, queue);
+    }
+    void tileGetAllForReadingOnDevices(LayoutConvert = LayoutConvert::None, int queue = -1)
+    {
+        for (int64_t j = 0; j < nt(); ++j)
+            for (int64_t i = 0; i < mt(); ++i)
+                if (tileIsLocal(i, j) && inStoredTriangle(i, j)) tileGet(i, j, 0, false, queue);
+        finishSet(0, queue);
+    }
+
+    /// Refreshes the origin instance from the Modified replica (BaseMatrix.hh:3190-3243).
+    void tileUpdateOrigin(int64_t i, int64_t j)
+    {
+        updateOrigin(i, j);
+        finishHostCopies();
+    }
+    void tileUpdateAllOrigin()
+    {
+        for (int64_t j = 0; j < nt(); ++j)
+            for (int64_t i = 0; i < mt(); ++i)
+                if (tileIsLocal(i, j) && inStoredTriangle(i, j) && tileExists(i, j)) updateOrigin(i, j);
+        finishHostCopies();
+    }
+
+    // ---- workspace -----------------------------------------------------------------------
+    /// gemmC.cc:57-60 / potrf.cc:69-71.  Queues and descriptor rings are created lazily by
+    /// the engine, so this only keeps the call sites compiling.
+    void allocateBatchArrays(int64_t batch_size = 0, int64_t num_arrays = 1)
+    {
+        for (int q = 0; q < num_arrays && q < Engine::MaxQueues; ++q)
+            Engine::instance().compute_stream(q);
+    }
+    void clearBatchArrays() {}
+    int64_t getMaxDeviceTiles(int device)
+    {
+        int64_t count = 0;
+        for (int64_t j = 0; j < nt(); ++j)
+            for (int64_t i = 0; i < mt(); ++i)
+                if (tileIsLocal(i, j) && inStoredTriangle(i, j)) ++count;
+        return count;
+    }
+    /// Matrix.hh:745-768 / MatrixStorage.hh:697-757: make sure the pool holds a block for
+    /// every local tile not born on the device plus `extra` blocks for broadcast panels.
+    void reserveDeviceWorkspace(int64_t extra_blocks = -1)
+    {
+        if (num_devices() == 0) return;
+        int64_t need = 0;
+        if (origin_ != Target::Devices) need += getMaxDeviceTiles(0);
+        if (extra_blocks < 0) {
+            // (lookahead + 2) panels of one block row + one block column of remote tiles
+            extra_blocks = (storage_->comm_->size > 1) ? 4 * (storage_->mt_ + storage_->nt_) : 0;
+        }
+        need += extra_blocks;
+        int64_t have = (int64_t)storage_->memory_.available(0);
+        if (need > have) storage_->memory_.addDeviceBlocks(0, need - have);
+    }
+
+    /// MatrixStorage::ensureDeviceWorkspace (MatrixStorage.hh:759-790): at least `blocks`
+    /// free blocks in the pool, for broadcast panels and host-origin staging.  A matrix whose
+    /// tiles were born on the device of a single-rank run needs none.
+    void ensureDeviceWorkspace(int64_t blocks)
+    {
+        if (num_devices() == 0) return;
+        if (origin_ == Target::Devices && storage_->comm_->size == 1) return;
+        int64_t have = (int64_t)storage_->memory_.available(0);
+        if (blocks > have) storage_->memory_.addDeviceBlocks(0, blocks - have);
+    }
+
+    /// Erases tiles that are not local (received by broadcast) once their receive count
+    /// drops to zero (BaseMatrix.hh:3875-3937).
+    void releaseRemoteWorkspace(int64_t receive_count = 1)
+    {
+        for (int64_t j = 0; j < nt(); ++j)
+            for (int64_t i = 0; i < mt(); ++i)
+                if (!tileIsLocal(i, j)) releaseRemoteWorkspaceTile(i, j, receive_count);
+        storage_->flushErased();
+    }
+    void releaseRemoteWorkspaceTile(int64_t i, int64_t j, int64_t receive_count = 1)
+    {
+        auto* node = storage_->find(globalIndex(i, j));
+        if (!node) return;
+        node->receive_count -= receive_count;
+        if (node->receive_count <= 0) {
+            storage_->tileErase(globalIndex(i, j), 0);
+            storage_->tileErase(globalIndex(i, j), HostNum);
+        }
+    }
+    /// Erases workspace replicas of local tiles unless they hold the only valid copy
+    /// (MatrixStorage.hh:894-933).
+    void releaseLocalWorkspace()
+    {
+        for (int64_t j = 0; j < nt(); ++j)
+            for (int64_t i = 0; i < mt(); ++i)
+                if (tileIsLocal(i, j)) releaseLocalWorkspaceTile(i, j);
+        storage_->flushErased();
+    }
+    void releaseLocalWorkspaceTile(int64_t i, int64_t j)
+    {
+        auto* node = storage_->find(globalIndex(i, j));
+        if (!node) return;
+        if (node->dev && node->dev->workspace() && node->dev_state != MOSI::Modified
+            && node->host && node->host_state != MOSI::Invalid)
+            storage_->tileErase(globalIndex(i, j), 0);
+        else if (node->host && node->host->workspace() && node->host_state != MOSI::Modified
+                 && node->dev && node->dev_state != MOSI::Invalid)
+            storage_->tileErase(globalIndex(i, j), HostNum);
+    }
+    void releaseWorkspace()
+    {
+        releaseRemoteWorkspace(1 << 30);
+        releaseLocalWorkspace();
+    }
+    void clearWorkspace() { releaseWorkspace(); }
+
+    // ---- broadcasts ------------------------------------------------------------------------
+    /// Send tile (i, j) to every rank owning a tile of B (BaseMatrix.hh:1961-1990).
+    template <Target target = Target::Host>
+    void tileBcast(int64_t i, int64_t j, BaseMatrix<scalar_t> const& B,
+                   Layout layout = Layout::ColMajor, int tag = 0, int64_t life_factor = 1)
+    {
+        BcastList list;
+        list.push_back({i, j, {B}});
+        listBcast<target>(list, layout, tag, life_factor);
+    }
+
+    /// BaseMatrix.hh:2028-2106.  One NCCL group for the whole list, on the comm stream.
+    template <Target target = Target::Host>
+    void listBcast(BcastList& bcast_list, Layout layout = Layout::ColMajor, int tag = 0,
+                   int64_t life_factor = 1, bool is_shared = false)
+    {
+        BcastListTag tagged;
+        tagged.reserve(bcast_list.size());
+        for (auto& e : bcast_list)
+            tagged.push_back({std::get<0>(e), std::get<1>(e), std::get<2>(e), (int64_t)tag});
+        listBcastMT<target>(tagged, layout, life_factor, is_shared);
+    }
+
+    /// BaseMatrix.hh:2129-2213.  Tags are not needed: NCCL matches sends and receives in
+    /// issue order per pair of ranks, and every rank walks the list in the same order.
+    template <Target target = Target::Host>
+    void listBcastMT(BcastListTag& bcast_list, Layout layout = Layout::ColMajor,
+                     int64_t life_factor = 1, bool is_shared = false);
+
+    /// ranks owning at least one tile of this view (BaseMatrix.hh:3702-3756)
+    void getRanks(std::set<int>* bcast_set) const
+    {
+        for (int64_t j = 0; j < nt(); ++j)
+            for (int64_t i = 0; i < mt(); ++i)
+                if (inStoredTriangle(i, j)) bcast_set->insert(tileRank(i, j));
+    }
+
+    std::shared_ptr<MatrixStorage<scalar_t>> const& storage() const { return storage_; }
+
+protected:
+    /// general matrices store everything; trapezoid ones override through uplo_
+    bool inStoredTriangle(int64_t i, int64_t j) const
+    {
+        if (uplo_ == Uplo::General) return true;
+        Uplo u = uploLogical();
+        return u == Uplo::Lower ? i >= j : i <= j;
+    }
+
+    void tileGet(int64_t i, int64_t j, int device, bool modify, int queue);
+    void updateOrigin(int64_t i, int64_t j);
+    void finishHostCopies()
+    {
+        if (host_copies_pending_) {
+            Engine::instance().sync_comm();
+            host_copies_pending_ = false;
+        }
+    }
+    void finishSet(int device, int queue)
+    {
+        if (device == HostNum) { finishHostCopies(); return; }
+        if (device_copies_pending_) {
+            Engine::instance().mark_comm();
+            device_copies_pending_ = false;
+        }
+        if (queue >= 0) Engine::instance().queue_wait_comm(queue);
+    }
+
+    int64_t ioffset_, joffset_, mt_, nt_;
+    Uplo uplo_;
+    Op op_;
+    Layout layout_;
+    Target origin_;
+    std::shared_ptr<MatrixStorage<scalar_t>> storage_;
+    bool host_copies_pending_ = false;
+    bool device_copies_pending_ = false;
+
+    template <typename T> friend class BaseMatrix;
+};
+
+//------------------------------------------------------------------------------
+template <typename scalar_t>
+void BaseMatrix<scalar_t>::tileGet(int64_t i, int64_t j, int device, bool modify, int queue)
+{
+    Engine& eng = Engine::instance();
+    auto& node = storage_->at(globalIndex(i, j));
+    if (device == HostNum) {
+        if (!(node.host && node.host_state != MOSI::Invalid)) {
+            slate_assert(node.dev && node.dev_state != MOSI::Invalid);
+            if (!node.host) storage_->tileInsert(globalIndex(i, j), HostNum, TileKind::Workspace);
+            // device -> host: after the queue that produced the data
+            eng.comm_wait_queue(node.write_queue);
+            Tile<scalar_t>* s = node.dev;
+            Tile<scalar_t>* d = node.host;
+            slate_te_call(te_memcpy2d_async(d->data(), sizeof(scalar_t) * d->stride(), s->data(),
+                                            sizeof(scalar_t) * s->stride(),
+                                            sizeof(scalar_t) * s->mb(), s->nb(), TE_COPY_D2H,
+                                            eng.comm_stream()));
+            host_copies_pending_ = true;
+            node.host_state = MOSI::Shared;
+            if (node.dev_state == MOSI::Modified) node.dev_state = MOSI::Shared;
+        }
+        if (modify) {
+            node.host_state = MOSI::Modified;
+            if (node.dev) node.dev_state = MOSI::Invalid;
+        }
+        return;
+    }
+    // ---- device instance ----
+    if (node.dev && node.dev_state != MOSI::Invalid) {
+        // read-after-write / write-after-write across compute queues
+        if (queue >= 0 && node.write_queue >= 0 && node.write_queue != queue)
+            eng.queue_wait_queue(queue, node.write_queue);
+    }
+    else {
+        slate_assert(node.host && node.host_state != MOSI::Invalid);
+        if (!node.dev) storage_->tileInsert(globalIndex(i, j), 0, TileKind::Workspace);
+        Tile<scalar_t>* s = node.host;
+        Tile<scalar_t>* d = node.dev;
+        slate_te_call(te_memcpy2d_async(d->data(), sizeof(scalar_t) * d->stride(), s->data(),
+                                        sizeof(scalar_t) * s->stride(), sizeof(scalar_t) * s->mb(),
+                                        s->nb(), TE_COPY_H2D, eng.comm_stream()));
+        device_copies_pending_ = true;
+        node.dev_state = MOSI::Shared;
+        node.write_queue = -1;
+        if (node.host_state == MOSI::Modified) node.host_state = MOSI::Shared;
+    }
+    if (modify) {
+        node.dev_state = MOSI::Modified;
+        if (node.host) node.host_state = MOSI::Invalid;
+        if (queue >= 0) node.write_queue = queue;
+    }
+}
+
+template <typename scalar_t>
+void BaseMatrix<scalar_t>::updateOrigin(int64_t i, int64_t j)
+{
+    auto& node = storage_->at(globalIndex(i, j));
+    const bool host_is_origin = node.host && node.host->origin();
+    const bool dev_is_origin = node.dev && node.dev->origin();
+    if (host_is_origin && node.host_state == MOSI::Invalid)
+        tileGet(i, j, HostNum, false, -1);
+    else if (dev_is_origin && node.dev_state == MOSI::Invalid) {
+        tileGet(i, j, 0, false, -1);
+        device_copies_pending_ = false;
+        Engine::instance().mark_comm();
+    }
+}
+
+//------------------------------------------------------------------------------
+template <typename scalar_t>
+template <Target target>
+void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
+                                       int64_t life_factor, bool is_shared)
+{
+    Engine& eng = Engine::instance();
+    Comm* comm = storage_->comm_;
+    const int me = comm->rank;
+
+    if (comm->size == 1) {
+        // BaseMatrix.hh:2057-2097: with one rank the "broadcast" is the fetch onto the device
+        if (target == Target::Devices && num_devices() > 0) {
+            for (auto& e : bcast_list) {
+                int64_t i = std::get<0>(e), j = std::get<1>(e);
+                if (tileIsLocal(i, j)) tileGet(i, j, 0, false, -1);
+            }
+            finishSet(0, -1);
+        }
+        return;
+    }
+
+    slate_assert(comm->nccl != nullptr);
+    void* stream = eng.comm_stream();
+    bool any = false;
+    std::vector<char> in_set(comm->size);
+    for (auto& e : bcast_list) {
+        int64_t i = std::get<0>(e), j = std::get<1>(e);
+        auto& dests = std::get<2>(e);
+        const int root = tileRank(i, j);
+        std::fill(in_set.begin(), in_set.end(), 0);
+        for (auto const& B : dests) {
+            for (int64_t jj = 0; jj < B.nt(); ++jj)
+                for (int64_t ii = 0; ii < B.mt(); ++ii)
+                    if (B.inStoredTriangle(ii, jj)) in_set[B.tileRank(ii, jj)] = 1;
+        }
+        in_set[root] = 0;
+        if (me == root) {
+            bool has_dest = false;
+            for (int r = 0; r < comm->size; ++r) has_dest |= (in_set[r] != 0);
+            if (!has_dest) continue;
+            tileGet(i, j, 0, false, -1);
+            auto& node = storage_->at(globalIndex(i, j));
+            if (device_copies_pending_) { eng.mark_comm(); device_copies_pending_ = false; }
+            eng.comm_wait_queue(node.write_queue);
+            Tile<scalar_t>* t = node.dev;
+            if (!any) { slate_te_call(te_comm_group_start()); any = true; }
+            // device instances made by this library are contiguous (stride == mb)
+            slate_assert(t->isContiguous());
+            for (int r = 0; r < comm->size; ++r)
+                if (in_set[r])
+                    slate_te_call(te_comm_send(comm->nccl, t->data(), t->bytes(), r, stream));
+        }
+        else if (in_set[me]) {
+            // tilePrepareToReceive (MatrixStorage.hh:406-420): workspace tile on the device
+            auto* node = storage_->find(globalIndex(i, j));
+            if (!node || !node->dev)
+                storage_->tileInsert(globalIndex(i, j), 0, TileKind::Workspace);
+            auto& nd = storage_->at(globalIndex(i, j));
+            nd.receive_count += 1;
+            nd.dev_state = MOSI::Shared;
+            nd.write_queue = -1;
+            Tile<scalar_t>* t = nd.dev;
+            if (!any) { slate_te_call(te_comm_group_start()); any = true; }
+            slate_te_call(te_comm_recv(comm->nccl, t->data(), t->bytes(), root, stream));
+        }
+    }
+    if (any) {
+        slate_te_call(te_comm_group_end());
+        eng.mark_comm();
+    }
+}
+
+}  // namespace slate
+
+#endif

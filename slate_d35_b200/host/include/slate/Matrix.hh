@@ -1,0 +1,259 @@
+// slate/Matrix.hh -- Matrix, HermitianMatrix, SymmetricMatrix, TriangularMatrix over
+// BaseMatrix.  Constructors and factory functions keep the reference's argument lists
+// (include/slate/Matrix.hh:41-55, 355-520, 832-847; HermitianMatrix.hh;
+//  BaseTrapezoidMatrix.hh; TriangularMatrix.hh).
+#ifndef SLATE_B200_MATRIX_HH
+#define SLATE_B200_MATRIX_HH
+
+#include "slate/BaseMatrix.hh"
+
+namespace slate {
+
+//------------------------------------------------------------------------------
+template <typename scalar_t>
+class Matrix : public BaseMatrix<scalar_t> {
+public:
+    Matrix() : BaseMatrix<scalar_t>() {}
+
+    /// include/slate/Matrix.hh:41-55: m x n, square tiles nb, p x q grid (column-major ranks)
+    Matrix(int64_t m, int64_t n, int64_t nb, int p, int q, MPI_Comm comm)
+        : BaseMatrix<scalar_t>(m, n, nb, nb, GridOrder::Col, p, q, comm) {}
+    Matrix(int64_t m, int64_t n, int64_t mb, int64_t nb, GridOrder order, int p, int q,
+           MPI_Comm comm)
+        : BaseMatrix<scalar_t>(m, n, mb, nb, order, p, q, comm) {}
+
+    /// include/slate/Matrix.hh:355-384: view of a column-major host array; every rank
+    /// passes its own array and owns the tiles the grid assigns to it.
+    static Matrix fromLAPACK(int64_t m, int64_t n, scalar_t* A, int64_t lda, int64_t nb,
+                             int p, int q, MPI_Comm comm)
+    {
+        Matrix M(m, n, nb, p, q, comm);
+        M.origin_ = Target::Host;
+        for (int64_t j = 0; j < M.nt(); ++j)
+            for (int64_t i = 0; i < M.mt(); ++i)
+                if (M.tileIsLocal(i, j))
+                    M.tileInsert(i, j, HostNum, &A[i * nb + j * nb * lda], lda);
+        return M;
+    }
+
+    /// include/slate/Matrix.hh:486-520: 2D block-cyclic local array, ScaLAPACK layout.
+    static Matrix fromScaLAPACK(int64_t m, int64_t n, scalar_t* A, int64_t lda, int64_t nb,
+                                int p, int q, MPI_Comm comm)
+    {
+        Matrix M(m, n, nb, p, q, comm);
+        M.origin_ = Target::Host;
+        for (int64_t j = 0; j < M.nt(); ++j)
+            for (int64_t i = 0; i < M.mt(); ++i)
+                if (M.tileIsLocal(i, j))
+                    M.tileInsert(i, j, HostNum, &A[(i / p) * nb + (j / q) * nb * lda], lda);
+        return M;
+    }
+
+    /// include/slate/Matrix.hh:832-847: SLATE-owned tiles on the host or born on the device.
+    void insertLocalTiles(Target origin = Target::Host)
+    {
+        this->origin_ = origin;
+        const bool on_dev = (origin == Target::Devices);
+        if (on_dev) {
+            int64_t count = this->getMaxDeviceTiles(0);
+            int64_t have = (int64_t)this->storage_->memory_.available(0);
+            if (count > have) this->storage_->memory_.addDeviceBlocks(0, count - have);
+        }
+        for (int64_t j = 0; j < this->nt(); ++j)
+            for (int64_t i = 0; i < this->mt(); ++i)
+                if (this->tileIsLocal(i, j))
+                    this->tileInsert(i, j, on_dev ? 0 : HostNum);
+    }
+
+    Matrix sub(int64_t i1, int64_t i2, int64_t j1, int64_t j2)
+    {
+        return Matrix(*this, i1, i2, j1, j2);
+    }
+
+    Matrix(BaseMatrix<scalar_t> const& orig, int64_t i1, int64_t i2, int64_t j1, int64_t j2)
+        : BaseMatrix<scalar_t>(orig, i1, i2, j1, j2)
+    {
+        this->uplo_ = Uplo::General;
+    }
+};
+
+//------------------------------------------------------------------------------
+/// Upper or lower trapezoid storage: only tiles of the `uplo` triangle exist.
+template <typename scalar_t>
+class BaseTrapezoidMatrix : public BaseMatrix<scalar_t> {
+public:
+    BaseTrapezoidMatrix() : BaseMatrix<scalar_t>() {}
+
+    /// BaseTrapezoidMatrix.hh: off-diagonal block as a general matrix
+    Matrix<scalar_t> sub(int64_t i1, int64_t i2, int64_t j1, int64_t j2)
+    {
+        return Matrix<scalar_t>(*this, i1, i2, j1, j2);
+    }
+
+    void insertLocalTiles(Target origin = Target::Host)
+    {
+        this->origin_ = origin;
+        const bool on_dev = (origin == Target::Devices);
+        if (on_dev) {
+            int64_t count = this->getMaxDeviceTiles(0);
+            int64_t have = (int64_t)this->storage_->memory_.available(0);
+            if (count > have) this->storage_->memory_.addDeviceBlocks(0, count - have);
+        }
+        for (int64_t j = 0; j < this->nt(); ++j)
+            for (int64_t i = 0; i < this->mt(); ++i)
+                if (this->tileIsLocal(i, j) && this->inStoredTriangle(i, j))
+                    this->tileInsert(i, j, on_dev ? 0 : HostNum);
+    }
+
+protected:
+    BaseTrapezoidMatrix(Uplo uplo, int64_t m, int64_t n, int64_t nb, int p, int q, MPI_Comm comm)
+        : BaseMatrix<scalar_t>(m, n, nb, nb, GridOrder::Col, p, q, comm)
+    {
+        slate_assert(uplo == Uplo::Lower || uplo == Uplo::Upper);
+        this->uplo_ = uplo;
+    }
+    BaseTrapezoidMatrix(BaseMatrix<scalar_t> const& orig, int64_t i1, int64_t i2)
+        : BaseMatrix<scalar_t>(orig, i1, i2, i1, i2) {}
+    BaseTrapezoidMatrix(Uplo uplo, BaseMatrix<scalar_t> const& orig) : BaseMatrix<scalar_t>(orig)
+    {
+        this->uplo_ = uplo;
+    }
+
+    void insertUserTiles(scalar_t* A, int64_t lda, int64_t nb)
+    {
+        this->origin_ = Target::Host;
+        for (int64_t j = 0; j < this->nt(); ++j)
+            for (int64_t i = 0; i < this->mt(); ++i)
+                if (this->tileIsLocal(i, j) && this->inStoredTriangle(i, j))
+                    this->tileInsert(i, j, HostNum, &A[i * nb + j * nb * lda], lda);
+    }
+};
+
+//------------------------------------------------------------------------------
+template <typename scalar_t>
+class HermitianMatrix : public BaseTrapezoidMatrix<scalar_t> {
+public:
+    HermitianMatrix() {}
+    HermitianMatrix(Uplo uplo, int64_t n, int64_t nb, int p, int q, MPI_Comm comm)
+        : BaseTrapezoidMatrix<scalar_t>(uplo, n, n, nb, p, q, comm) {}
+
+    static HermitianMatrix fromLAPACK(Uplo uplo, int64_t n, scalar_t* A, int64_t lda, int64_t nb,
+                                      int p, int q, MPI_Comm comm)
+    {
+        HermitianMatrix M(uplo, n, nb, p, q, comm);
+        M.insertUserTiles(A, lda, nb);
+        return M;
+    }
+
+    /// diagonal block [i1..i2] x [i1..i2]
+    HermitianMatrix sub(int64_t i1, int64_t i2) { return HermitianMatrix(*this, i1, i2); }
+    Matrix<scalar_t> sub(int64_t i1, int64_t i2, int64_t j1, int64_t j2)
+    {
+        return BaseTrapezoidMatrix<scalar_t>::sub(i1, i2, j1, j2);
+    }
+
+    HermitianMatrix(BaseMatrix<scalar_t> const& orig, int64_t i1, int64_t i2)
+        : BaseTrapezoidMatrix<scalar_t>(orig, i1, i2) {}
+    HermitianMatrix(Uplo uplo, BaseMatrix<scalar_t> const& orig)
+        : BaseTrapezoidMatrix<scalar_t>(uplo, orig) {}
+};
+
+template <typename scalar_t>
+class SymmetricMatrix : public BaseTrapezoidMatrix<scalar_t> {
+public:
+    SymmetricMatrix() {}
+    SymmetricMatrix(Uplo uplo, int64_t n, int64_t nb, int p, int q, MPI_Comm comm)
+        : BaseTrapezoidMatrix<scalar_t>(uplo, n, n, nb, p, q, comm) {}
+    static SymmetricMatrix fromLAPACK(Uplo uplo, int64_t n, scalar_t* A, int64_t lda, int64_t nb,
+                                      int p, int q, MPI_Comm comm)
+    {
+        SymmetricMatrix M(uplo, n, nb, p, q, comm);
+        M.insertUserTiles(A, lda, nb);
+        return M;
+    }
+    SymmetricMatrix sub(int64_t i1, int64_t i2) { return SymmetricMatrix(*this, i1, i2); }
+    Matrix<scalar_t> sub(int64_t i1, int64_t i2, int64_t j1, int64_t j2)
+    {
+        return BaseTrapezoidMatrix<scalar_t>::sub(i1, i2, j1, j2);
+    }
+    SymmetricMatrix(BaseMatrix<scalar_t> const& orig, int64_t i1, int64_t i2)
+        : BaseTrapezoidMatrix<scalar_t>(orig, i1, i2) {}
+};
+
+template <typename scalar_t>
+class TriangularMatrix : public BaseTrapezoidMatrix<scalar_t> {
+public:
+    TriangularMatrix() : diag_(Diag::NonUnit) {}
+    TriangularMatrix(Uplo uplo, Diag diag, int64_t n, int64_t nb, int p, int q, MPI_Comm comm)
+        : BaseTrapezoidMatrix<scalar_t>(uplo, n, n, nb, p, q, comm), diag_(diag) {}
+
+    static TriangularMatrix fromLAPACK(Uplo uplo, Diag diag, int64_t n, scalar_t* A, int64_t lda,
+                                       int64_t nb, int p, int q, MPI_Comm comm)
+    {
+        TriangularMatrix M(uplo, diag, n, nb, p, q, comm);
+        M.insertUserTiles(A, lda, nb);
+        return M;
+    }
+
+    /// TriangularMatrix.hh: conversion sharing the tiles (potrf.cc:113-114)
+    TriangularMatrix(Diag diag, BaseTrapezoidMatrix<scalar_t> const& orig)
+        : BaseTrapezoidMatrix<scalar_t>(orig), diag_(diag) {}
+
+    Diag diag() const { return diag_; }
+    TriangularMatrix sub(int64_t i1, int64_t i2)
+    {
+        TriangularMatrix T(*this);
+        static_cast<BaseMatrix<scalar_t>&>(T) = BaseTrapezoidMatrix<scalar_t>(*this, i1, i2);
+        return T;
+    }
+    Matrix<scalar_t> sub(int64_t i1, int64_t i2, int64_t j1, int64_t j2)
+    {
+        return BaseTrapezoidMatrix<scalar_t>::sub(i1, i2, j1, j2);
+    }
+
+protected:
+    Diag diag_;
+};
+
+//------------------------------------------------------------------------------
+// include/slate/BaseMatrix.hh:3247-3290: shallow views with the op toggled.
+namespace detail {
+template <typename M>
+struct ViewAccess : public M {
+    static void set_op(M& A, Op op) { static_cast<ViewAccess&>(A).op_ = op; }
+};
+}  // namespace detail
+
+template <typename MatrixType>
+MatrixType transpose(MatrixType& A)
+{
+    using scalar_t = decltype(A(0, 0)(0, 0));
+    MatrixType AT = A;
+    Op op = A.op();
+    if (op == Op::NoTrans) op = Op::Trans;
+    else if (op == Op::Trans || !is_complex<scalar_t>::value) op = Op::NoTrans;
+    else slate_error("unsupported operation, results in conjugate-no-transpose");
+    detail::ViewAccess<MatrixType>::set_op(AT, op);
+    return AT;
+}
+template <typename MatrixType>
+MatrixType transpose(MatrixType&& A) { return transpose(A); }
+
+template <typename MatrixType>
+MatrixType conj_transpose(MatrixType& A)
+{
+    using scalar_t = decltype(A(0, 0)(0, 0));
+    MatrixType AT = A;
+    Op op = A.op();
+    if (op == Op::NoTrans) op = Op::ConjTrans;
+    else if (op == Op::ConjTrans || !is_complex<scalar_t>::value) op = Op::NoTrans;
+    else slate_error("unsupported operation, results in conjugate-no-transpose");
+    detail::ViewAccess<MatrixType>::set_op(AT, op);
+    return AT;
+}
+template <typename MatrixType>
+MatrixType conj_transpose(MatrixType&& A) { return conj_transpose(A); }
+
+}  // namespace slate
+
+#endif

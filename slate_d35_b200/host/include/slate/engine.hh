@@ -1,0 +1,182 @@
+// slate/engine.hh -- per-process runtime under the matrix classes: the device, its
+// streams ("queues"), event-ordered hand-offs, descriptor staging, deferred release of
+// workspace tiles, the communicator, and slate::Memory (the device-tile pool).
+//
+// Mirrors, B200-first, what the reference spreads over
+//   MatrixStorage::initQueues / compute_queue / comm_queue / allocateBatchArrays
+//       (include/slate/internal/MatrixStorage.hh:198-245, 574-696)
+//   slate::Memory (include/slate/internal/Memory.hh:29-101, src/core/Memory.cc)
+//   the MPI communicator argument of every matrix constructor.
+// Differences by design: one process drives ONE GPU (one rank per GPU, NCCL between
+// them); nothing synchronises the host per step -- ordering between the comm stream
+// and the compute queues is by CUDA events, and a workspace tile goes back to the pool
+// only once the kernels that read it have finished (deferred release).
+//
+// Everything device-side goes through the C ABI of include/tile_engine.h.
+#ifndef SLATE_B200_ENGINE_HH
+#define SLATE_B200_ENGINE_HH
+
+#include "slate/enums.hh"
+#include "tile_engine.h"
+
+#include <deque>
+#include <functional>
+#include <mutex>
+#include <vector>
+
+namespace slate {
+
+#define slate_te_call(expr)                                                             \
+    do {                                                                                \
+        int te_status_ = (expr);                                                        \
+        if (te_status_ != TE_OK)                                                        \
+            throw slate::EngineException(#expr, te_status_, te_last_error(), __func__,  \
+                                         __FILE__, __LINE__);                           \
+    } while (0)
+
+//------------------------------------------------------------------------------
+/// Stand-in for MPI_Comm: the set of ranks (one per GPU) and their NCCL communicator.
+/// A single-rank Comm needs no NCCL.
+struct Comm {
+    te_comm* nccl = nullptr;
+    int rank = 0;
+    int size = 1;
+};
+
+/// MPI_COMM_WORLD of this process (set by slate::initialize; single rank by default).
+Comm* comm_world();
+Comm* comm_self();
+
+//------------------------------------------------------------------------------
+/// include/slate/internal/Memory.hh:29-101.  Fixed-size blocks, block_size bytes each.
+class Memory {
+public:
+    Memory(size_t block_size);
+    ~Memory();
+    Memory(Memory const&) = delete;
+
+    void addHostBlocks(int64_t) {}
+    void addDeviceBlocks(int device, int64_t num_blocks);
+    void clearHostBlocks() {}
+    void clearDeviceBlocks(int device);
+
+    void* alloc(int device, size_t size);
+    void free(void* block, int device);
+
+    size_t available(int device) const;
+    size_t capacity(int device) const;
+    size_t allocated(int device) const { return capacity(device) - available(device); }
+    size_t block_size() const { return block_size_; }
+
+    static int num_devices_;
+
+private:
+    size_t block_size_;
+    te_pool* pool_;       // the one device this process drives
+    int device_;
+};
+
+//------------------------------------------------------------------------------
+class Engine {
+public:
+    static Engine& instance();
+
+    /// Binds this process to a CUDA device (default: $LOCAL_RANK, else 0) and creates
+    /// the comm stream.  Idempotent for the same device.
+    void initialize(int device = -1);
+    bool initialized() const { return initialized_; }
+    int device() const { return device_; }
+    int num_devices() const { return te_device_count() > 0 ? 1 : 0; }
+
+    void* comm_stream();
+    void* compute_stream(int queue);
+    static const int MaxQueues = 16;
+
+    // ---- event-ordered hand-offs ----
+    /// call after enqueueing work on queue q / on the comm stream
+    void mark_queue(int q);
+    void mark_comm();
+    /// make queue q wait for everything enqueued so far on the comm stream / other queue
+    void queue_wait_comm(int q);
+    void queue_wait_queue(int q, int other);
+    /// make the comm stream wait for everything enqueued so far on queue q
+    void comm_wait_queue(int q);
+    void comm_wait_all_queues();
+    void sync_comm();
+    void sync_queue(int q);
+    void sync_all();
+
+    // ---- descriptor staging: pinned host + device ring per queue ----
+    struct DescSlot {
+        void* host = nullptr;
+        void* dev = nullptr;
+        size_t capacity = 0;
+        void* event = nullptr;
+        bool pending = false;
+    };
+    /// A slot with room for `bytes`; blocks only if the ring is full of unfinished launches.
+    DescSlot& acquire_desc(int q, size_t bytes);
+    /// Uploads the first `bytes` of the slot on queue q.
+    void upload_desc(int q, DescSlot& slot, size_t bytes);
+    /// Call after the kernel that reads the slot was launched on queue q.
+    void retire_desc(int q, DescSlot& slot);
+
+    /// Device scratch private to queue q (grows; stream-ordered reuse on that queue).
+    void* scratch(int q, size_t bytes);
+    /// One device int per (queue, slot) for potrf's info.
+    int* info_slot(int index);
+
+    // ---- deferred actions (release of workspace tiles) ----
+    /// Runs fn once everything enqueued so far on the given queues (bit q) and, if
+    /// `comm`, on the comm stream has finished.  Polled by poll_deferred().
+    void defer(unsigned queue_mask, bool comm, std::function<void()> fn);
+    void poll_deferred(bool wait_oldest = false);
+    void drain_deferred();
+
+    // ---- timing across all streams ----
+    void* timer_begin();             // joins all streams, returns start event
+    float timer_end(void* start);    // joins all streams, returns elapsed ms (synchronises)
+
+    void finalize();
+
+private:
+    Engine() {}
+    struct Deferred { std::vector<void*> events; std::function<void()> fn; };
+    void* new_event(bool timing = false);
+    void recycle_event(void* ev);
+
+    bool initialized_ = false;
+    int device_ = 0;
+    void* comm_stream_ = nullptr;
+    void* comm_event_ = nullptr;
+    uint64_t comm_seq_ = 0;
+    void* queue_[MaxQueues] = {};
+    void* queue_event_[MaxQueues] = {};
+    uint64_t queue_seq_[MaxQueues] = {};
+    uint64_t queue_saw_comm_[MaxQueues] = {};
+    static const int RingDepth = 4;
+    DescSlot ring_[MaxQueues][RingDepth];
+    int ring_next_[MaxQueues] = {};
+    void* scratch_[MaxQueues] = {};
+    size_t scratch_bytes_[MaxQueues] = {};
+    int* info_base_ = nullptr;
+    std::deque<Deferred> deferred_;
+    std::vector<void*> event_pool_;
+    std::recursive_mutex mu_;
+};
+
+/// Process set-up for the harness: device binding and (size > 1) the NCCL communicator.
+/// nccl_id: TE_COMM_ID_BYTES bytes from te_comm_unique_id on rank 0, or nullptr if size == 1.
+void initialize(int device, int rank, int size, const void* nccl_id);
+void finalize();
+
+}  // namespace slate
+
+// The reference's constructors take an MPI_Comm; keep the call text compiling.
+#ifndef MPI_VERSION
+typedef slate::Comm* MPI_Comm;
+#define MPI_COMM_WORLD (slate::comm_world())
+#define MPI_COMM_SELF  (slate::comm_self())
+#endif
+
+#endif

@@ -1,0 +1,60 @@
+// slate/slate.hh -- public drivers of the B200 engine: slate::gemm and slate::potrf with
+// the reference's signatures (include/slate/slate.hh:189-194, 764-767) and the
+// simplified-API aliases (include/slate/simplified_api.hh:30-37, 560-570).
+#ifndef SLATE_B200_SLATE_HH
+#define SLATE_B200_SLATE_HH
+
+#include "slate/internal.hh"
+
+namespace slate {
+
+/// C = alpha A B + beta C.  gemmC SUMMA (src/gemm.cc:66-88, src/gemmC.cc:29-191).
+/// Options: Target (only Target::Devices is built), Lookahead (default 1).
+template <typename scalar_t>
+void gemm(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t beta,
+          Matrix<scalar_t>& C, Options const& opts = Options());
+
+/// Cholesky factorisation A = L L^H (lower) or U^H U (upper), in place
+/// (src/potrf.cc:23-210, 262-281).  Returns info: 0, or i if the leading minor of order i
+/// is not positive definite.  Options: Target, Lookahead (default 1), HoldLocalWorkspace.
+template <typename scalar_t>
+int64_t potrf(HermitianMatrix<scalar_t>& A, Options const& opts = Options());
+
+// ---- simplified API -----------------------------------------------------------------------
+template <typename scalar_t>
+void multiply(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t beta,
+              Matrix<scalar_t>& C, Options const& opts = Options())
+{
+    gemm(alpha, A, B, beta, C, opts);
+}
+
+template <typename scalar_t>
+int64_t chol_factor(HermitianMatrix<scalar_t>& A, Options const& opts = Options())
+{
+    return potrf(A, opts);
+}
+
+// ---- harness helpers (not part of the reference surface) --------------------------------
+/// Fills the local tiles with matgen's "rand" family (matgen/generate_type_rand.hh:40-135):
+/// entry (i, j) is a pure function of (seed, i, j); `dominant` adds n to the diagonal.
+/// Device-origin tiles are generated on the device (te_matgen_tile), host-origin tiles
+/// are generated on the device and copied back, so both see identical bits.
+template <typename scalar_t>
+void generate_rand(BaseMatrix<scalar_t>& A, int64_t seed, bool dominant, int dist = 1);
+
+/// sum over local stored tiles of |a_ij|^2 (lower/upper triangle only for trapezoid
+/// matrices, diagonal tiles masked accordingly); not reduced over ranks.
+template <typename scalar_t>
+double local_sumsq(BaseMatrix<scalar_t>& A);
+
+/// || A0 - L L^H ||_F^2 over this rank's tiles of the lower triangle, where L is the
+/// factor held in A (lower) and A0 is regenerated from (seed, dominant).  Uses n^3/3
+/// flops of the engine's own GEMM; the north-star backward-error metric
+/// ||A - L L^H|| / (n ||A||) is assembled from it by the caller.
+template <typename scalar_t>
+double potrf_residual_sumsq(HermitianMatrix<scalar_t>& A, int64_t seed, bool dominant,
+                            double* a0_sumsq);
+
+}  // namespace slate
+
+#endif

@@ -1,0 +1,410 @@
+// c_api.cc -- C entry points of the host library for the Python harness (tests, bench,
+// smoke).  They play the role of the reference's generated C API
+// (include/slate/c_api/slate.h, src/c_api/wrappers.cc): opaque matrix handles, the two
+// drivers, and -- for unit-level parity -- the internal ops the reference's
+// unit_test/test_internal_blas.cc calls directly.  Every call returns 0 or a negative
+// status; sb_last_error() holds the exception text.
+#include "slate/slate.hh"
+
+#include <cstring>
+#include <memory>
+#include <string>
+
+using namespace slate;
+typedef std::complex<double> zdouble;
+
+namespace {
+
+thread_local std::string g_error;
+
+enum Kind { General = 0, Hermitian = 1, Symmetric = 2, Triangular = 3 };
+
+struct Handle {
+    int dtype;     // TE_F64 / TE_C64
+    int kind;
+    std::shared_ptr<void> obj;
+};
+
+template <typename T> Matrix<T>& as_general(Handle* h) { return *static_cast<Matrix<T>*>(h->obj.get()); }
+template <typename T> HermitianMatrix<T>& as_herm(Handle* h) { return *static_cast<HermitianMatrix<T>*>(h->obj.get()); }
+template <typename T> SymmetricMatrix<T>& as_symm(Handle* h) { return *static_cast<SymmetricMatrix<T>*>(h->obj.get()); }
+template <typename T> TriangularMatrix<T>& as_tri(Handle* h) { return *static_cast<TriangularMatrix<T>*>(h->obj.get()); }
+template <typename T> BaseMatrix<T>& as_base(Handle* h)
+{
+    switch (h->kind) {
+        case Hermitian: return as_herm<T>(h);
+        case Symmetric: return as_symm<T>(h);
+        case Triangular: return as_tri<T>(h);
+        default: return as_general<T>(h);
+    }
+}
+
+template <typename F>
+int guarded(F&& f)
+{
+    try {
+        f();
+        return 0;
+    }
+    catch (std::exception const& e) {
+        g_error = e.what();
+        return -1;
+    }
+    catch (...) {
+        g_error = "unknown exception";
+        return -2;
+    }
+}
+
+template <typename T>
+T scalar_from(const double* p)
+{
+    if constexpr (is_complex<T>::value) return T(p[0], p[1]);
+    else return p[0];
+}
+
+template <typename M>
+M view_op(M& A, int op)
+{
+    if (op == 'T') return transpose(A);
+    if (op == 'C') return conj_transpose(A);
+    return A;
+}
+
+Options make_opts(int target, int lookahead)
+{
+    return {{Option::Target, Target(char(target))}, {Option::Lookahead, (int64_t)lookahead}};
+}
+
+template <typename T>
+void create(Handle* h, int kind, int uplo, int diag, int64_t m, int64_t n, int64_t nb, int p, int q,
+            int origin, T* host, int64_t ld)
+{
+    Uplo u = (uplo == 'U') ? Uplo::Upper : Uplo::Lower;
+    Diag d = (diag == 'U') ? Diag::Unit : Diag::NonUnit;
+    Target org = (origin == 'D') ? Target::Devices : Target::Host;
+    MPI_Comm comm = MPI_COMM_WORLD;
+    if (p * q == 1 && comm->size > 1) comm = MPI_COMM_SELF;
+    switch (kind) {
+        case General: {
+            auto M = host ? std::make_shared<Matrix<T>>(Matrix<T>::fromLAPACK(m, n, host, ld, nb, p, q, comm))
+                          : std::make_shared<Matrix<T>>(m, n, nb, p, q, comm);
+            if (!host) M->insertLocalTiles(org);
+            h->obj = M;
+            break;
+        }
+        case Hermitian: {
+            auto M = host ? std::make_shared<HermitianMatrix<T>>(
+                                HermitianMatrix<T>::fromLAPACK(u, n, host, ld, nb, p, q, comm))
+                          : std::make_shared<HermitianMatrix<T>>(u, n, nb, p, q, comm);
+            if (!host) M->insertLocalTiles(org);
+            h->obj = M;
+            break;
+        }
+        case Symmetric: {
+            auto M = host ? std::make_shared<SymmetricMatrix<T>>(
+                                SymmetricMatrix<T>::fromLAPACK(u, n, host, ld, nb, p, q, comm))
+                          : std::make_shared<SymmetricMatrix<T>>(u, n, nb, p, q, comm);
+            if (!host) M->insertLocalTiles(org);
+            h->obj = M;
+            break;
+        }
+        case Triangular: {
+            auto M = host ? std::make_shared<TriangularMatrix<T>>(
+                                TriangularMatrix<T>::fromLAPACK(u, d, n, host, ld, nb, p, q, comm))
+                          : std::make_shared<TriangularMatrix<T>>(u, d, n, nb, p, q, comm);
+            if (!host) M->insertLocalTiles(org);
+            h->obj = M;
+            break;
+        }
+        default: slate_error("unknown matrix kind");
+    }
+}
+
+/// local tiles <-> a LAPACK-layout host array of the whole matrix (harness only)
+template <typename T>
+void copy_all(Handle* h, T* host, int64_t ld, bool to_host)
+{
+    BaseMatrix<T>& A = as_base<T>(h);
+    Engine& eng = Engine::instance();
+    auto st = A.storage();
+    const bool trap = A.uploPhysical() != Uplo::General;
+    std::vector<int64_t> roff(A.mt() + 1, 0), coff(A.nt() + 1, 0);
+    for (int64_t i = 0; i < A.mt(); ++i) roff[i + 1] = roff[i] + A.tileMb(i);
+    for (int64_t j = 0; j < A.nt(); ++j) coff[j + 1] = coff[j] + A.tileNb(j);
+    for (int64_t j = 0; j < A.nt(); ++j)
+        for (int64_t i = 0; i < A.mt(); ++i) {
+            if (!A.tileIsLocal(i, j)) continue;
+            if (trap && (A.uploLogical() == Uplo::Lower ? i < j : i > j)) continue;
+            T* hp = host + roff[i] + coff[j] * ld;
+            if (to_host) {
+                A.tileGetForReading(i, j, HostNum);
+                auto t = A(i, j, HostNum);
+                t.op(Op::NoTrans);
+                for (int64_t c = 0; c < t.nb(); ++c)
+                    std::memcpy(hp + c * ld, t.data() + c * t.stride(), sizeof(T) * t.mb());
+            }
+            else {
+                A.tileGetForWriting(i, j, HostNum);
+                auto t = A(i, j, HostNum);
+                t.op(Op::NoTrans);
+                for (int64_t c = 0; c < t.nb(); ++c)
+                    std::memcpy(t.data() + c * t.stride(), hp + c * ld, sizeof(T) * t.mb());
+            }
+        }
+    if (!to_host && A.origin() == Target::Devices) {
+        A.tileUpdateAllOrigin();
+        eng.sync_all();
+        // host staging copies are not needed any more
+        for (int64_t j = 0; j < A.nt(); ++j)
+            for (int64_t i = 0; i < A.mt(); ++i)
+                if (A.tileIsLocal(i, j) && A.tileExists(i, j, HostNum) && A.tileExists(i, j, 0))
+                    A.tileErase(i, j, HostNum);
+    }
+    if (to_host && A.origin() == Target::Devices) {
+        for (int64_t j = 0; j < A.nt(); ++j)
+            for (int64_t i = 0; i < A.mt(); ++i)
+                if (A.tileIsLocal(i, j) && A.tileExists(i, j, HostNum) && A.tileExists(i, j, 0))
+                    A.tileErase(i, j, HostNum);
+    }
+}
+
+}  // namespace
+
+#define DISPATCH(h, call_d, call_z)          \
+    do {                                     \
+        if ((h)->dtype == TE_C64) { call_z; } \
+        else { call_d; }                     \
+    } while (0)
+
+extern "C" {
+
+const char* sb_last_error(void) { return g_error.c_str(); }
+
+int sb_initialize(int device, int rank, int size, const void* nccl_id)
+{
+    return guarded([&] { slate::initialize(device, rank, size, nccl_id); });
+}
+
+int sb_finalize(void)
+{
+    return guarded([&] { slate::finalize(); });
+}
+
+int sb_sync(void)
+{
+    return guarded([&] { Engine::instance().sync_all(); });
+}
+
+int sb_matrix_create(int dtype, int kind, int uplo, int diag, int64_t m, int64_t n, int64_t nb,
+                     int p, int q, int origin, void* host, int64_t ld, void** out)
+{
+    return guarded([&] {
+        auto h = std::make_unique<Handle>();
+        h->dtype = dtype;
+        h->kind = kind;
+        if (dtype == TE_C64) create<zdouble>(h.get(), kind, uplo, diag, m, n, nb, p, q, origin, (zdouble*)host, ld);
+        else create<double>(h.get(), kind, uplo, diag, m, n, nb, p, q, origin, (double*)host, ld);
+        *out = h.release();
+    });
+}
+
+int sb_matrix_destroy(void* handle)
+{
+    return guarded([&] {
+        Engine::instance().sync_all();
+        delete static_cast<Handle*>(handle);
+    });
+}
+
+int sb_matrix_generate(void* handle, int64_t seed, int dominant, int dist)
+{
+    Handle* h = static_cast<Handle*>(handle);
+    return guarded([&] {
+        DISPATCH(h, generate_rand(as_base<double>(h), seed, dominant != 0, dist),
+                 generate_rand(as_base<zdouble>(h), seed, dominant != 0, dist));
+    });
+}
+
+int sb_matrix_to_host(void* handle, void* out, int64_t ld)
+{
+    Handle* h = static_cast<Handle*>(handle);
+    return guarded([&] {
+        DISPATCH(h, copy_all<double>(h, (double*)out, ld, true),
+                 copy_all<zdouble>(h, (zdouble*)out, ld, true));
+    });
+}
+
+int sb_matrix_from_host(void* handle, const void* in, int64_t ld)
+{
+    Handle* h = static_cast<Handle*>(handle);
+    return guarded([&] {
+        DISPATCH(h, copy_all<double>(h, (double*)in, ld, false),
+                 copy_all<zdouble>(h, (zdouble*)in, ld, false));
+    });
+}
+
+int sb_matrix_sumsq(void* handle, double* out)
+{
+    Handle* h = static_cast<Handle*>(handle);
+    return guarded([&] {
+        DISPATCH(h, *out = local_sumsq(as_base<double>(h)), *out = local_sumsq(as_base<zdouble>(h)));
+    });
+}
+
+int sb_pool_stats(void* handle, int64_t* available, int64_t* capacity)
+{
+    Handle* h = static_cast<Handle*>(handle);
+    return guarded([&] {
+        if (h->dtype == TE_C64) {
+            auto& mem = as_base<zdouble>(h).storage()->memory_;
+            *available = (int64_t)mem.available(0);  *capacity = (int64_t)mem.capacity(0);
+        }
+        else {
+            auto& mem = as_base<double>(h).storage()->memory_;
+            *available = (int64_t)mem.available(0);  *capacity = (int64_t)mem.capacity(0);
+        }
+    });
+}
+
+/// C = alpha op(A) op(B) + beta C through slate::gemm; *ms = device time of the call.
+int sb_gemm(int opa, int opb, const double* alpha, void* A, void* B, const double* beta, void* C,
+            int lookahead, int target, float* ms)
+{
+    Handle *ha = (Handle*)A, *hb = (Handle*)B, *hc = (Handle*)C;
+    return guarded([&] {
+        Engine& eng = Engine::instance();
+        Options opts = make_opts(target, lookahead);
+        void* t0 = ms ? eng.timer_begin() : nullptr;
+        if (hc->dtype == TE_C64) {
+            auto opA = view_op(as_general<zdouble>(ha), opa);
+            auto opB = view_op(as_general<zdouble>(hb), opb);
+            gemm(scalar_from<zdouble>(alpha), opA, opB, scalar_from<zdouble>(beta),
+                 as_general<zdouble>(hc), opts);
+        }
+        else {
+            auto opA = view_op(as_general<double>(ha), opa);
+            auto opB = view_op(as_general<double>(hb), opb);
+            gemm(alpha[0], opA, opB, beta[0], as_general<double>(hc), opts);
+        }
+        if (ms) *ms = eng.timer_end(t0);
+    });
+}
+
+int sb_potrf(void* A, int lookahead, int target, int64_t* info, float* ms)
+{
+    Handle* h = (Handle*)A;
+    return guarded([&] {
+        Engine& eng = Engine::instance();
+        Options opts = make_opts(target, lookahead);
+        void* t0 = ms ? eng.timer_begin() : nullptr;
+        DISPATCH(h, *info = potrf(as_herm<double>(h), opts), *info = potrf(as_herm<zdouble>(h), opts));
+        if (ms) *ms = eng.timer_end(t0);
+    });
+}
+
+int sb_potrf_residual(void* A, int64_t seed, int dominant, double* resid_sumsq, double* a0_sumsq)
+{
+    Handle* h = (Handle*)A;
+    return guarded([&] {
+        DISPATCH(h,
+                 *resid_sumsq = potrf_residual_sumsq(as_herm<double>(h), seed, dominant != 0, a0_sumsq),
+                 *resid_sumsq = potrf_residual_sumsq(as_herm<zdouble>(h), seed, dominant != 0, a0_sumsq));
+    });
+}
+
+// ---- internal ops, as unit_test/test_internal_blas.cc drives them ------------------------
+int sb_internal_gemm(int opa, int opb, int opc, const double* alpha, void* A, void* B,
+                     const double* beta, void* C, int target, int queue)
+{
+    Handle *ha = (Handle*)A, *hb = (Handle*)B, *hc = (Handle*)C;
+    return guarded([&] {
+        if (target != 'D') slate_not_implemented("only Target::Devices is built");
+        if (hc->dtype == TE_C64) {
+            auto opA = view_op(as_general<zdouble>(ha), opa);
+            auto opB = view_op(as_general<zdouble>(hb), opb);
+            auto opC = view_op(as_general<zdouble>(hc), opc);
+            internal::gemm<Target::Devices>(scalar_from<zdouble>(alpha), std::move(opA), std::move(opB),
+                                            scalar_from<zdouble>(beta), std::move(opC),
+                                            Layout::ColMajor, 0, queue);
+        }
+        else {
+            auto opA = view_op(as_general<double>(ha), opa);
+            auto opB = view_op(as_general<double>(hb), opb);
+            auto opC = view_op(as_general<double>(hc), opc);
+            internal::gemm<Target::Devices>(alpha[0], std::move(opA), std::move(opB), beta[0],
+                                            std::move(opC), Layout::ColMajor, 0, queue);
+        }
+    });
+}
+
+int sb_internal_herk(int opa, int opc, double alpha, void* A, double beta, void* C, int queue)
+{
+    Handle *ha = (Handle*)A, *hc = (Handle*)C;
+    return guarded([&] {
+        if (hc->dtype == TE_C64) {
+            auto opA = view_op(as_general<zdouble>(ha), opa);
+            auto opC = view_op(as_herm<zdouble>(hc), opc);
+            if (opC.uplo() == Uplo::Upper) opC = conj_transpose(opC);     // src/herk.cc
+            internal::herk<Target::Devices>(alpha, std::move(opA), beta, std::move(opC), 0, queue);
+        }
+        else {
+            auto opA = view_op(as_general<double>(ha), opa);
+            auto opC = view_op(as_herm<double>(hc), opc);
+            if (opC.uplo() == Uplo::Upper) opC = conj_transpose(opC);
+            internal::herk<Target::Devices>(alpha, std::move(opA), beta, std::move(opC), 0, queue);
+        }
+    });
+}
+
+int sb_internal_syrk(int opa, int opc, const double* alpha, void* A, const double* beta, void* C,
+                     int queue)
+{
+    Handle *ha = (Handle*)A, *hc = (Handle*)C;
+    return guarded([&] {
+        if (hc->dtype == TE_C64) {
+            auto opA = view_op(as_general<zdouble>(ha), opa);
+            auto opC = view_op(as_symm<zdouble>(hc), opc);
+            if (opC.uplo() == Uplo::Upper) opC = transpose(opC);          // src/syrk.cc
+            internal::syrk<Target::Devices>(scalar_from<zdouble>(alpha), std::move(opA),
+                                            scalar_from<zdouble>(beta), std::move(opC), 0, queue);
+        }
+        else {
+            auto opA = view_op(as_general<double>(ha), opa);
+            auto opC = view_op(as_symm<double>(hc), opc);
+            if (opC.uplo() == Uplo::Upper) opC = transpose(opC);
+            internal::syrk<Target::Devices>(alpha[0], std::move(opA), beta[0], std::move(opC), 0, queue);
+        }
+    });
+}
+
+int sb_internal_trsm(int side, int opa, int opb, const double* alpha, void* A, void* B, int queue)
+{
+    Handle *ha = (Handle*)A, *hb = (Handle*)B;
+    return guarded([&] {
+        Side s = (side == 'L') ? Side::Left : Side::Right;
+        if (hb->dtype == TE_C64) {
+            auto opA = view_op(as_tri<zdouble>(ha), opa);
+            auto opB = view_op(as_general<zdouble>(hb), opb);
+            internal::trsm<Target::Devices>(s, scalar_from<zdouble>(alpha), std::move(opA),
+                                            std::move(opB), 0, Layout::ColMajor, queue);
+        }
+        else {
+            auto opA = view_op(as_tri<double>(ha), opa);
+            auto opB = view_op(as_general<double>(hb), opb);
+            internal::trsm<Target::Devices>(s, alpha[0], std::move(opA), std::move(opB), 0,
+                                            Layout::ColMajor, queue);
+        }
+    });
+}
+
+int sb_internal_potrf(void* A, int queue, int64_t* info)
+{
+    Handle* h = (Handle*)A;
+    return guarded([&] {
+        DISPATCH(h, *info = internal::potrf<Target::Devices>(as_herm<double>(h).sub(0, 0), 0, queue),
+                 *info = internal::potrf<Target::Devices>(as_herm<zdouble>(h).sub(0, 0), 0, queue));
+    });
+}
+
+}  // extern "C"

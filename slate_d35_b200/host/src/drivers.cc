@@ -1,0 +1,391 @@
+// drivers.cc -- slate::gemm (gemmC SUMMA) and slate::potrf on the tile engine, plus the
+// harness helpers declared in slate/slate.hh.
+//
+// The loop structure follows the reference drivers (src/gemmC.cc:29-191,
+// src/potrf.cc:23-210); what differs is the execution model.  The reference builds an
+// OpenMP task DAG whose tasks block in queue->sync(); here ONE host thread enqueues every
+// step on CUDA streams and never waits: dependencies between the panel queue, the
+// lookahead queues, the trailing-update queue and the NCCL broadcasts are events derived
+// from which queue last wrote each tile (BaseMatrix::tileGet), and broadcast workspace is
+// recycled by deferred release.  Lookahead keeps its meaning: how many block columns the
+// broadcasts / panel factorisations run ahead of the trailing update.
+#include "slate/slate.hh"
+
+#include <cmath>
+
+namespace slate {
+
+//------------------------------------------------------------------------------
+template <typename scalar_t>
+void gemm(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t beta,
+          Matrix<scalar_t>& C, Options const& opts)
+{
+    if (get_target(opts) != Target::Devices)
+        slate_not_implemented("slate::gemm: this build implements Target::Devices only "
+                              "(there is no CPU fallback)");
+    const int64_t lookahead = get_option<int64_t>(opts, Option::Lookahead, 1);
+    const Layout layout = Layout::ColMajor;
+    const scalar_t one = 1.0;
+    const int queue_0 = 0;
+    using BcastListTag = typename Matrix<scalar_t>::BcastListTag;
+
+    slate_assert(A.mt() == C.mt());
+    slate_assert(B.nt() == C.nt());
+    slate_assert(A.nt() == B.mt());
+    slate_assert(C.op() == Op::NoTrans);
+    const int64_t kt = A.nt();
+
+    // src/gemmC.cc:57-60
+    C.allocateBatchArrays();
+    C.reserveDeviceWorkspace(0);
+    A.ensureDeviceWorkspace((lookahead + 3) * A.mt());
+    B.ensureDeviceWorkspace((lookahead + 3) * B.nt());
+
+    // fetch_C (src/gemmC.cc:70-74)
+    C.tileGetAllForWritingOnDevices(LayoutConvert(layout), queue_0);
+
+    if (kt == 0) {
+        // nothing to accumulate; the reference's loop does not run either
+        C.tileUpdateAllOrigin();
+        Engine::instance().sync_all();
+        return;
+    }
+
+    // send block column k of A along the process rows and block row k of B along the
+    // process columns that own C (src/gemmC.cc:78-110, 143-157)
+    auto bcast = [&](int64_t k) {
+        BcastListTag list_A, list_B;
+        for (int64_t i = 0; i < A.mt(); ++i)
+            list_A.push_back({i, k, {C.sub(i, i, 0, C.nt() - 1)}, i});
+        A.template listBcastMT<Target::Devices>(list_A, layout);
+        for (int64_t j = 0; j < B.nt(); ++j)
+            list_B.push_back({k, j, {C.sub(0, C.mt() - 1, j, j)}, j});
+        B.template listBcastMT<Target::Devices>(list_B, layout);
+    };
+
+    for (int64_t k = 0; k <= lookahead && k < kt; ++k)
+        bcast(k);
+
+    for (int64_t k = 0; k < kt; ++k) {
+        if (k > 0 && k + lookahead < kt)
+            bcast(k + lookahead);
+
+        // src/gemmC.cc:113-171: beta only on the first block outer product
+        internal::gemm<Target::Devices>(
+            alpha, A.sub(0, A.mt() - 1, k, k), B.sub(k, k, 0, B.nt() - 1),
+            k == 0 ? beta : one, std::move(C), layout, 0, queue_0);
+
+        // src/gemmC.cc:173-185: drop the panel (returns to the pool when the update is done)
+        auto A_panel = A.sub(0, A.mt() - 1, k, k);
+        A_panel.releaseRemoteWorkspace();
+        A_panel.releaseLocalWorkspace();
+        auto B_panel = B.sub(k, k, 0, B.nt() - 1);
+        B_panel.releaseRemoteWorkspace();
+        B_panel.releaseLocalWorkspace();
+        Engine::instance().poll_deferred();
+    }
+
+    // src/gemmC.cc:187-190
+    C.tileUpdateAllOrigin();
+    C.releaseWorkspace();
+    Engine::instance().sync_all();
+}
+
+//------------------------------------------------------------------------------
+template <typename scalar_t>
+int64_t potrf(HermitianMatrix<scalar_t>& A_in, Options const& opts)
+{
+    if (get_target(opts) != Target::Devices)
+        slate_not_implemented("slate::potrf: this build implements Target::Devices only "
+                              "(there is no CPU fallback)");
+    using real_t = real_type<scalar_t>;
+    using BcastListTag = typename Matrix<scalar_t>::BcastListTag;
+    const scalar_t one = 1.0;
+    const Layout layout = Layout::ColMajor;
+    const int64_t lookahead = get_option<int64_t>(opts, Option::Lookahead, 1);
+    const bool hold_local_workspace = get_option<int64_t>(opts, Option::HoldLocalWorkspace, 0) != 0;
+    Engine& eng = Engine::instance();
+
+    // trailing update on queue 0; potrf + trsm of the panel on queue 1 (high priority);
+    // lookahead column j of step k on queue 2 + (j - k - 1)   (src/potrf.cc:34-36, 152-174)
+    const int queue_trail = 0, queue_panel = 1, queue_la0 = 2;
+    slate_assert(lookahead >= 0 && queue_la0 + lookahead <= Engine::MaxQueues - 1);
+
+    // if upper, change to lower (src/potrf.cc:45-47)
+    HermitianMatrix<scalar_t> A = A_in;
+    if (A.uplo() == Uplo::Upper)
+        A = conj_transpose(A);
+    const int64_t A_nt = A.nt();
+    slate_assert(A_nt < 4095);
+
+    A.allocateBatchArrays(0, queue_la0 + lookahead);
+    A.reserveDeviceWorkspace();
+    if (A_nt == 0) return 0;
+
+    // info of step k stays on the device (the reference copies it back and syncs each step)
+    slate_te_call(te_memset_async(eng.info_slot(0), 0, sizeof(int) * A_nt,
+                                  eng.compute_stream(queue_panel)));
+    eng.mark_queue(queue_panel);
+
+    for (int64_t k = 0; k < A_nt; ++k) {
+        // ---- panel (src/potrf.cc:90-133) ----
+        internal::potrf<Target::Devices>(A.sub(k, k), 0, queue_panel, eng.info_slot((int)k));
+
+        if (k + 1 <= A_nt - 1) {
+            // send A(k, k) down col A(k+1:nt-1, k)
+            A.template tileBcast<Target::Devices>(k, k, A.sub(k + 1, A_nt - 1, k, k), layout);
+
+            // A(k+1:nt-1, k) * A(k, k)^{-H}
+            auto Akk = A.sub(k, k);
+            auto Tkk = TriangularMatrix<scalar_t>(Diag::NonUnit, Akk);
+            internal::trsm<Target::Devices>(Side::Right, one, conj_transpose(Tkk),
+                                            A.sub(k + 1, A_nt - 1, k, k), 0, layout, queue_panel);
+
+            // send A(i, k) across row A(i, k+1:i) and down col A(i:nt-1, i)
+            BcastListTag bcast_list_A;
+            for (int64_t i = k + 1; i < A_nt; ++i)
+                bcast_list_A.push_back({i, k, {A.sub(i, i, k + 1, i), A.sub(i, A_nt - 1, i, i)}, i});
+            A.template listBcastMT<Target::Devices>(bcast_list_A, layout);
+        }
+
+        // ---- lookahead columns first: the next panel waits for them (src/potrf.cc:156-177)
+        for (int64_t j = k + 1; j < k + 1 + lookahead && j < A_nt; ++j) {
+            const int queue_j = queue_la0 + (int)(j - k - 1);
+            // A(j, j) -= A(j, k) * A(j, k)^H
+            internal::herk<Target::Devices>(real_t(-1.0), A.sub(j, j, k, k), real_t(1.0),
+                                            A.sub(j, j), 0, queue_j, layout);
+            // A(j+1:nt, j) -= A(j+1:nt-1, k) * A(j, k)^H
+            if (j + 1 <= A_nt - 1) {
+                auto Ajk = A.sub(j, j, k, k);
+                internal::gemm<Target::Devices>(-one, A.sub(j + 1, A_nt - 1, k, k),
+                                                conj_transpose(Ajk), one,
+                                                A.sub(j + 1, A_nt - 1, j, j), layout, 0, queue_j);
+            }
+        }
+
+        // ---- trailing submatrix (src/potrf.cc:136-149) ----
+        if (k + 1 + lookahead < A_nt) {
+            internal::herk<Target::Devices>(real_t(-1.0), A.sub(k + 1 + lookahead, A_nt - 1, k, k),
+                                            real_t(1.0), A.sub(k + 1 + lookahead, A_nt - 1), 0,
+                                            queue_trail, layout);
+        }
+
+        // ---- release the panel (src/potrf.cc:179-192); blocks return when step k is done
+        {
+            auto panel = A.sub(k, A_nt - 1, k, k);
+            panel.releaseRemoteWorkspace();
+            if (A.origin() != Target::Devices) {
+                panel.tileUpdateAllOrigin();
+                panel.releaseLocalWorkspace();
+            }
+        }
+        eng.poll_deferred();
+    }
+
+    A.tileUpdateAllOrigin();
+    if (!hold_local_workspace)
+        A.releaseWorkspace();
+    eng.sync_all();
+
+    // first failing step -> LAPACK info (src/potrf.cc:104-105, 208)
+    std::vector<int> step_info(A_nt, 0);
+    slate_te_call(te_memcpy_async(step_info.data(), eng.info_slot(0), sizeof(int) * A_nt,
+                                  TE_COPY_D2H, eng.comm_stream()));
+    eng.sync_comm();
+    int64_t info = 0, kk = 0;
+    for (int64_t k = 0; k < A_nt; ++k) {
+        if (step_info[k] != 0 && A.tileIsLocal(k, k)) {
+            info = kk + step_info[k];
+            break;
+        }
+        kk += A.tileNb(k);
+    }
+    internal::reduce_info(&info, A.mpiComm());
+    return info;
+}
+
+//------------------------------------------------------------------------------
+namespace {
+template <typename scalar_t>
+std::vector<int64_t> row_offsets(BaseMatrix<scalar_t>& A)
+{
+    std::vector<int64_t> off(A.mt() + 1, 0);
+    for (int64_t i = 0; i < A.mt(); ++i) off[i + 1] = off[i] + A.tileMb(i);
+    return off;
+}
+template <typename scalar_t>
+std::vector<int64_t> col_offsets(BaseMatrix<scalar_t>& A)
+{
+    std::vector<int64_t> off(A.nt() + 1, 0);
+    for (int64_t j = 0; j < A.nt(); ++j) off[j + 1] = off[j] + A.tileNb(j);
+    return off;
+}
+template <typename scalar_t>
+bool stored(BaseMatrix<scalar_t>& A, int64_t i, int64_t j)
+{
+    if (A.uploPhysical() == Uplo::General) return true;
+    return A.uploLogical() == Uplo::Lower ? i >= j : i <= j;
+}
+}  // namespace
+
+template <typename scalar_t>
+void generate_rand(BaseMatrix<scalar_t>& A, int64_t seed, bool dominant, int dist)
+{
+    slate_assert(A.op() == Op::NoTrans);
+    Engine& eng = Engine::instance();
+    const int dtype = internal::te_dtype_of<scalar_t>::value;
+    auto roff = row_offsets(A);
+    auto coff = col_offsets(A);
+    const double diag_add = dominant ? (double)roff[A.mt()] : 0.0;
+    void* stream = eng.compute_stream(0);
+    void* staging = nullptr;
+    for (int64_t j = 0; j < A.nt(); ++j) {
+        for (int64_t i = 0; i < A.mt(); ++i) {
+            if (!A.tileIsLocal(i, j) || !stored(A, i, j)) continue;
+            const int mb = (int)A.tileMb(i), nb = (int)A.tileNb(j);
+            if (A.tileExists(i, j, 0) && A.origin() == Target::Devices) {
+                auto T = A(i, j, 0);
+                slate_te_call(te_matgen_tile(eng.device(), stream, dtype, dist, seed, mb, nb, roff[i],
+                                             coff[j], T.data(), T.stride(), diag_add));
+                A.tileModified(i, j, 0, 0);
+            }
+            else {
+                // host-origin tile: same bits, produced on the device and copied back
+                if (!staging)
+                    staging = eng.scratch(Engine::MaxQueues - 2,
+                                          sizeof(scalar_t) * (size_t)A.storage()->mb_ * A.storage()->nb_);
+                auto T = A(i, j, HostNum);
+                slate_te_call(te_matgen_tile(eng.device(), stream, dtype, dist, seed, mb, nb, roff[i],
+                                             coff[j], staging, mb, diag_add));
+                slate_te_call(te_memcpy2d_async(T.data(), sizeof(scalar_t) * T.stride(), staging,
+                                                sizeof(scalar_t) * mb, sizeof(scalar_t) * mb, nb,
+                                                TE_COPY_D2H, stream));
+                eng.sync_queue(0);
+                A.tileModified(i, j, HostNum);
+            }
+        }
+    }
+    eng.mark_queue(0);
+    eng.sync_queue(0);
+}
+
+template <typename scalar_t>
+double local_sumsq(BaseMatrix<scalar_t>& A)
+{
+    Engine& eng = Engine::instance();
+    const int dtype = internal::te_dtype_of<scalar_t>::value;
+    void* stream = eng.compute_stream(0);
+    double* acc = (double*)eng.scratch(Engine::MaxQueues - 3, sizeof(double));
+    slate_te_call(te_memset_async(acc, 0, sizeof(double), stream));
+    const bool trapezoid = A.uploPhysical() != Uplo::General;
+    for (int64_t j = 0; j < A.nt(); ++j) {
+        for (int64_t i = 0; i < A.mt(); ++i) {
+            if (!A.tileIsLocal(i, j) || !stored(A, i, j)) continue;
+            A.tileGetForReading(i, j, 0, LayoutConvert::None, 0);
+            Engine::instance().mark_comm();
+            Engine::instance().queue_wait_comm(0);
+            auto T = A(i, j, 0);
+            T.op(Op::NoTrans);
+            const int mb = (int)T.mb(), nb = (int)T.nb();
+            if (!trapezoid) {
+                slate_te_call(te_tile_sumsq(eng.device(), stream, dtype, 0, mb, nb, T.data(),
+                                            T.stride(), acc));
+            }
+            else if (i == j) {
+                // full Hermitian norm: diagonal once, strict triangle twice
+                const bool lower = A.uploPhysical() == Uplo::Lower;
+                slate_te_call(te_tile_sumsq(eng.device(), stream, dtype, lower ? 1 : 2, mb, nb,
+                                            T.data(), T.stride(), acc));
+                if (lower)
+                    slate_te_call(te_tile_sumsq(eng.device(), stream, dtype, 3, mb, nb, T.data(),
+                                                T.stride(), acc));
+                else
+                    slate_error("local_sumsq: upper storage not supported");
+            }
+            else {
+                slate_te_call(te_tile_sumsq(eng.device(), stream, dtype, 0, mb, nb, T.data(),
+                                            T.stride(), acc));
+                slate_te_call(te_tile_sumsq(eng.device(), stream, dtype, 0, mb, nb, T.data(),
+                                            T.stride(), acc));
+            }
+        }
+    }
+    double result = 0;
+    slate_te_call(te_memcpy_async(&result, acc, sizeof(double), TE_COPY_D2H, stream));
+    eng.mark_queue(0);
+    eng.sync_queue(0);
+    return result;
+}
+
+template <typename scalar_t>
+double potrf_residual_sumsq(HermitianMatrix<scalar_t>& A, int64_t seed, bool dominant,
+                            double* a0_sumsq)
+{
+    using real_t = real_type<scalar_t>;
+    using BcastListTag = typename Matrix<scalar_t>::BcastListTag;
+    slate_assert(A.uploPhysical() == Uplo::Lower && A.op() == Op::NoTrans);
+    slate_assert(A.origin() == Target::Devices);
+    Engine& eng = Engine::instance();
+    const int dtype = internal::te_dtype_of<scalar_t>::value;
+    auto st = A.storage();
+    const int64_t n = st->n_, nb = st->nb_;
+    const int64_t nt = A.nt();
+    const Layout layout = Layout::ColMajor;
+
+    // R = A0, regenerated bit for bit
+    HermitianMatrix<scalar_t> R(Uplo::Lower, n, nb, st->p_, st->q_, st->comm_);
+    R.insertLocalTiles(Target::Devices);
+    R.reserveDeviceWorkspace();
+    generate_rand(R, seed, dominant, 1);
+    if (a0_sumsq) *a0_sumsq = local_sumsq(R);
+
+    // shadow matrix holding clean copies of block column k of L (strict upper of L(k,k) zeroed)
+    Matrix<scalar_t> Lm(n, n, nb, st->p_, st->q_, st->comm_);
+    Lm.reserveDeviceWorkspace(3 * nt + 8);
+    void* stream = eng.compute_stream(0);
+    for (int64_t k = 0; k < nt; ++k) {
+        for (int64_t i = k; i < nt; ++i) {
+            if (!A.tileIsLocal(i, k)) continue;
+            A.tileGetForReading(i, k, 0, LayoutConvert::None, 0);
+            auto src = A(i, k, 0);
+            Lm.tileInsert(i, k, 0);
+            auto dst = Lm(i, k, 0);
+            slate_assert(src.stride() == src.mb() && dst.stride() == dst.mb());
+            slate_te_call(te_memcpy_async(dst.data(), src.data(), src.bytes(), TE_COPY_D2D, stream));
+            if (i == k)
+                slate_te_call(te_tile_keep_triangle(eng.device(), stream, dtype, TE_UPLO_LOWER,
+                                                    (int)dst.mb(), (int)dst.nb(), dst.data(),
+                                                    dst.stride()));
+            Lm.tileModified(i, k, 0, 0);
+        }
+        eng.mark_queue(0);
+        BcastListTag list;
+        for (int64_t i = k; i < nt; ++i)
+            list.push_back({i, k, {R.sub(i, i, k, i), R.sub(i, nt - 1, i, i)}, i});
+        Lm.template listBcastMT<Target::Devices>(list, layout);
+        // R(k:, k:) -= L(k:, k) L(k:, k)^H
+        internal::herk<Target::Devices>(real_t(-1.0), Lm.sub(k, nt - 1, k, k), real_t(1.0),
+                                        R.sub(k, nt - 1), 0, 0, layout);
+        auto panel = Lm.sub(k, nt - 1, k, k);
+        panel.releaseRemoteWorkspace();
+        for (int64_t i = k; i < nt; ++i)
+            if (Lm.tileIsLocal(i, k)) Lm.tileErase(i, k, 0);
+        Lm.storage()->flushErased();
+        eng.poll_deferred();
+    }
+    double r = local_sumsq(R);
+    eng.sync_all();
+    return r;
+}
+
+//------------------------------------------------------------------------------
+#define INSTANTIATE(T)                                                                        \
+    template void gemm<T>(T, Matrix<T>&, Matrix<T>&, T, Matrix<T>&, Options const&);           \
+    template int64_t potrf<T>(HermitianMatrix<T>&, Options const&);                            \
+    template void generate_rand<T>(BaseMatrix<T>&, int64_t, bool, int);                        \
+    template double local_sumsq<T>(BaseMatrix<T>&);                                            \
+    template double potrf_residual_sumsq<T>(HermitianMatrix<T>&, int64_t, bool, double*);
+INSTANTIATE(double)
+INSTANTIATE(std::complex<double>)
+
+}  // namespace slate

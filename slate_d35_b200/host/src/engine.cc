@@ -1,0 +1,374 @@
+// engine.cc -- see slate/engine.hh.
+#include "slate/engine.hh"
+
+#include <cstdlib>
+#include <cstring>
+
+namespace slate {
+
+static Comm g_world;
+static Comm g_self;
+Comm* comm_world() { return &g_world; }
+Comm* comm_self() { return &g_self; }
+
+//------------------------------------------------------------------------------
+int Memory::num_devices_ = -1;
+
+Memory::Memory(size_t block_size) : block_size_(block_size), pool_(nullptr)
+{
+    Engine& eng = Engine::instance();
+    if (!eng.initialized()) eng.initialize();
+    device_ = eng.device();
+    if (num_devices_ < 0) num_devices_ = eng.num_devices();
+    if (num_devices_ > 0)
+        slate_te_call(te_pool_create(device_, block_size_ ? block_size_ : 256, &pool_));
+}
+
+Memory::~Memory()
+{
+    if (pool_) te_pool_destroy(pool_);
+}
+
+/// src/core/Memory.cc:63-72: one cudaMalloc of num_blocks blocks.
+void Memory::addDeviceBlocks(int device, int64_t num_blocks)
+{
+    slate_assert(pool_ != nullptr);
+    slate_te_call(te_pool_reserve(pool_, num_blocks));
+}
+
+void Memory::clearDeviceBlocks(int device)
+{
+    if (pool_) slate_te_call(te_pool_clear(pool_));
+}
+
+/// src/core/Memory.cc:118-141: host = new[], device = pop a block (grow by one if empty).
+void* Memory::alloc(int device, size_t size)
+{
+    if (device == HostNum)
+        return new char[size];
+    slate_assert(size <= block_size_);
+    slate_assert(pool_ != nullptr);
+    void* block = nullptr;
+    slate_te_call(te_pool_alloc(pool_, &block));
+    return block;
+}
+
+void Memory::free(void* block, int device)
+{
+    if (device == HostNum) {
+        delete[] (char*)block;
+        return;
+    }
+    slate_te_call(te_pool_free(pool_, block));
+}
+
+size_t Memory::available(int device) const
+{
+    if (device == HostNum || !pool_) return 0;
+    size_t a = 0;
+    te_pool_stats(pool_, &a, nullptr, nullptr);
+    return a;
+}
+
+size_t Memory::capacity(int device) const
+{
+    if (device == HostNum || !pool_) return 0;
+    size_t c = 0;
+    te_pool_stats(pool_, nullptr, &c, nullptr);
+    return c;
+}
+
+//------------------------------------------------------------------------------
+Engine& Engine::instance()
+{
+    static Engine e;
+    return e;
+}
+
+void Engine::initialize(int device)
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    if (device < 0) {
+        const char* lr = std::getenv("LOCAL_RANK");
+        device = lr ? std::atoi(lr) : 0;
+        int n = te_device_count();
+        if (n > 0) device %= n;
+    }
+    if (initialized_) {
+        slate_assert(device == device_);
+        return;
+    }
+    device_ = device;
+    initialized_ = true;
+    if (te_device_count() == 0)
+        return;     // host-only process: matrices can exist, device paths throw
+    slate_te_call(te_stream_create(device_, 1, &comm_stream_));
+    slate_te_call(te_event_create(device_, 0, &comm_event_));
+    void* p = nullptr;
+    slate_te_call(te_device_malloc(device_, sizeof(int) * 4096, &p));
+    info_base_ = (int*)p;
+}
+
+void* Engine::comm_stream()
+{
+    slate_assert(comm_stream_ != nullptr);
+    return comm_stream_;
+}
+
+void* Engine::compute_stream(int q)
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    slate_assert(q >= 0 && q < MaxQueues);
+    if (!queue_[q]) {
+        // queue 1 is the panel queue of potrf: high priority so that it overtakes the
+        // trailing update on the SMs it needs
+        slate_te_call(te_stream_create(device_, q == 1 ? 1 : 0, &queue_[q]));
+        slate_te_call(te_event_create(device_, 0, &queue_event_[q]));
+    }
+    return queue_[q];
+}
+
+void Engine::mark_queue(int q)
+{
+    void* s = compute_stream(q);
+    slate_te_call(te_event_record(queue_event_[q], s));
+    ++queue_seq_[q];
+}
+
+void Engine::mark_comm()
+{
+    slate_te_call(te_event_record(comm_event_, comm_stream()));
+    ++comm_seq_;
+}
+
+void Engine::queue_wait_comm(int q)
+{
+    void* s = compute_stream(q);
+    if (comm_seq_ == 0 || queue_saw_comm_[q] == comm_seq_) return;
+    slate_te_call(te_stream_wait_event(s, comm_event_));
+    queue_saw_comm_[q] = comm_seq_;
+}
+
+void Engine::queue_wait_queue(int q, int other)
+{
+    if (q == other || other < 0 || !queue_[other] || queue_seq_[other] == 0) return;
+    slate_te_call(te_stream_wait_event(compute_stream(q), queue_event_[other]));
+}
+
+void Engine::comm_wait_queue(int q)
+{
+    if (q < 0 || !queue_[q] || queue_seq_[q] == 0) return;
+    slate_te_call(te_stream_wait_event(comm_stream(), queue_event_[q]));
+}
+
+void Engine::comm_wait_all_queues()
+{
+    for (int q = 0; q < MaxQueues; ++q) comm_wait_queue(q);
+}
+
+void Engine::sync_comm() { slate_te_call(te_stream_sync(device_, comm_stream())); }
+void Engine::sync_queue(int q) { if (queue_[q]) slate_te_call(te_stream_sync(device_, queue_[q])); }
+
+void Engine::sync_all()
+{
+    if (te_device_count() == 0) return;
+    slate_te_call(te_device_sync(device_));
+    drain_deferred();
+}
+
+Engine::DescSlot& Engine::acquire_desc(int q, size_t bytes)
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    compute_stream(q);
+    DescSlot& s = ring_[q][ring_next_[q]];
+    ring_next_[q] = (ring_next_[q] + 1) % RingDepth;
+    if (s.pending) {
+        slate_te_call(te_event_sync(s.event));
+        s.pending = false;
+    }
+    if (s.capacity < bytes) {
+        if (s.host) slate_te_call(te_host_free_pinned(s.host));
+        if (s.dev) slate_te_call(te_device_free(device_, s.dev));
+        size_t cap = bytes + bytes / 4 + 4096;
+        slate_te_call(te_host_alloc_pinned(cap, &s.host));
+        slate_te_call(te_device_malloc(device_, cap, &s.dev));
+        s.capacity = cap;
+    }
+    if (!s.event) slate_te_call(te_event_create(device_, 0, &s.event));
+    return s;
+}
+
+void Engine::upload_desc(int q, DescSlot& s, size_t bytes)
+{
+    slate_te_call(te_memcpy_async(s.dev, s.host, bytes, TE_COPY_H2D, compute_stream(q)));
+}
+
+void Engine::retire_desc(int q, DescSlot& s)
+{
+    slate_te_call(te_event_record(s.event, compute_stream(q)));
+    s.pending = true;
+}
+
+void* Engine::scratch(int q, size_t bytes)
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    if (scratch_bytes_[q] < bytes) {
+        if (scratch_[q]) {
+            // the old buffer may still be in use by launches on this queue
+            sync_queue(q);
+            slate_te_call(te_device_free(device_, scratch_[q]));
+        }
+        size_t cap = bytes + bytes / 2;
+        slate_te_call(te_device_malloc(device_, cap, &scratch_[q]));
+        scratch_bytes_[q] = cap;
+    }
+    return scratch_[q];
+}
+
+int* Engine::info_slot(int index)
+{
+    slate_assert(index >= 0 && index < 4096 && info_base_);
+    return info_base_ + index;
+}
+
+void* Engine::new_event(bool timing)
+{
+    if (!timing && !event_pool_.empty()) {
+        void* e = event_pool_.back();
+        event_pool_.pop_back();
+        return e;
+    }
+    void* e = nullptr;
+    slate_te_call(te_event_create(device_, timing ? 1 : 0, &e));
+    return e;
+}
+
+void Engine::recycle_event(void* ev) { event_pool_.push_back(ev); }
+
+void Engine::defer(unsigned queue_mask, bool comm, std::function<void()> fn)
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    Deferred d;
+    d.fn = std::move(fn);
+    for (int q = 0; q < MaxQueues; ++q) {
+        if ((queue_mask >> q) & 1u) {
+            if (!queue_[q] || queue_seq_[q] == 0) continue;
+            void* e = new_event();
+            slate_te_call(te_event_record(e, queue_[q]));
+            d.events.push_back(e);
+        }
+    }
+    if (comm && comm_stream_) {
+        void* e = new_event();
+        slate_te_call(te_event_record(e, comm_stream_));
+        d.events.push_back(e);
+    }
+    if (d.events.empty()) {
+        d.fn();
+        return;
+    }
+    deferred_.push_back(std::move(d));
+}
+
+void Engine::poll_deferred(bool wait_oldest)
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    while (!deferred_.empty()) {
+        Deferred& d = deferred_.front();
+        bool done = true;
+        for (void* e : d.events) {
+            if (wait_oldest) {
+                slate_te_call(te_event_sync(e));
+            }
+            else if (te_event_query_done(e) != 1) {
+                done = false;
+                break;
+            }
+        }
+        if (!done) break;
+        for (void* e : d.events) recycle_event(e);
+        auto fn = std::move(d.fn);
+        deferred_.pop_front();
+        fn();
+        wait_oldest = false;
+    }
+}
+
+void Engine::drain_deferred()
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    while (!deferred_.empty())
+        poll_deferred(true);
+}
+
+void* Engine::timer_begin()
+{
+    sync_all();
+    void* e = new_event(true);
+    slate_te_call(te_event_record(e, compute_stream(0)));
+    // every other stream starts after the start event
+    for (int q = 1; q < MaxQueues; ++q)
+        if (queue_[q]) slate_te_call(te_stream_wait_event(queue_[q], e));
+    slate_te_call(te_stream_wait_event(comm_stream(), e));
+    return e;
+}
+
+float Engine::timer_end(void* start)
+{
+    void* s0 = compute_stream(0);
+    for (int q = 1; q < MaxQueues; ++q) {
+        if (queue_[q]) {
+            void* e = new_event();
+            slate_te_call(te_event_record(e, queue_[q]));
+            slate_te_call(te_stream_wait_event(s0, e));
+            recycle_event(e);
+        }
+    }
+    {
+        void* e = new_event();
+        slate_te_call(te_event_record(e, comm_stream()));
+        slate_te_call(te_stream_wait_event(s0, e));
+        recycle_event(e);
+    }
+    void* stop = new_event(true);
+    slate_te_call(te_event_record(stop, s0));
+    slate_te_call(te_event_sync(stop));
+    float ms = 0;
+    slate_te_call(te_event_elapsed_ms(start, stop, &ms));
+    te_event_destroy(start);
+    te_event_destroy(stop);
+    drain_deferred();
+    return ms;
+}
+
+void Engine::finalize()
+{
+    if (!initialized_ || te_device_count() == 0) return;
+    sync_all();
+}
+
+//------------------------------------------------------------------------------
+void initialize(int device, int rank, int size, const void* nccl_id)
+{
+    Engine::instance().initialize(device);
+    g_world.rank = rank;
+    g_world.size = size;
+    if (size > 1 && g_world.nccl == nullptr) {
+        slate_assert(nccl_id != nullptr);
+        slate_te_call(te_comm_init_rank(nccl_id, TE_COMM_ID_BYTES, size, rank,
+                                        Engine::instance().device(), &g_world.nccl));
+    }
+}
+
+void finalize()
+{
+    Engine::instance().finalize();
+    if (g_world.nccl) {
+        te_comm_destroy(g_world.nccl);
+        g_world.nccl = nullptr;
+    }
+    g_world.rank = 0;
+    g_world.size = 1;
+}
+
+}  // namespace slate

@@ -1,0 +1,371 @@
+// internal_ops.cc -- Target::Devices overloads of the internal Level-3 operations.
+// See slate/internal.hh.  Reference files: src/internal/internal_gemm.cc:355-518,
+// internal_herk.cc:351-535, internal_syrk.cc:346-527, internal_trsm.cc:132-261,
+// internal_potrf.cc:57-81, internal_batch.hh:169-394.
+#include "slate/internal.hh"
+
+#include <cstring>
+#include <limits>
+
+namespace slate {
+namespace internal {
+
+namespace {
+
+// Tiles are handed to the engine in 8 x 8 super-blocks of the local (row, column) index
+// space: the CTAs that run concurrently then share at most 8 A tiles and 8 B tiles
+// (32 MiB at nb = 512), which stay resident in the 126 MB L2 while 64 C tiles stream.
+const int64_t SuperBlock = 8;
+
+struct DescBatch {
+    std::vector<te_tile_desc> descs;
+    int32_t max_m = 0, max_n = 0;
+    void add(const void* a, int64_t lda, const void* b, int64_t ldb, void* c, int64_t ldc,
+             int64_t m, int64_t n, int64_t k, int flags)
+    {
+        te_tile_desc d;
+        d.a = a;  d.b = b;  d.c = c;
+        d.m = (int32_t)m;  d.n = (int32_t)n;  d.k = (int32_t)k;
+        d.lda = (int32_t)lda;  d.ldb = (int32_t)ldb;  d.ldc = (int32_t)ldc;
+        d.flags = flags;  d.reserved = 0;
+        descs.push_back(d);
+        if (d.m > max_m) max_m = d.m;
+        if (d.n > max_n) max_n = d.n;
+    }
+};
+
+template <typename scalar_t>
+void launch_batch(DescBatch& batch, int q, Op opa, Op opb, scalar_t alpha, scalar_t beta)
+{
+    if (batch.descs.empty()) return;
+    Engine& eng = Engine::instance();
+    const int dtype = te_dtype_of<scalar_t>::value;
+    void* stream = eng.compute_stream(q);
+    if ((int)batch.descs.size() <= TE_MAX_INLINE_DESC) {
+        // few tiles (panel / lookahead calls): descriptors ride in the kernel parameters
+        slate_te_call(te_gemm_inline(eng.device(), stream, dtype, int(opa), int(opb), &alpha, &beta,
+                                     batch.descs.data(), (int)batch.descs.size()));
+    }
+    else {
+        size_t bytes = batch.descs.size() * sizeof(te_tile_desc);
+        Engine::DescSlot& slot = eng.acquire_desc(q, bytes);
+        std::memcpy(slot.host, batch.descs.data(), bytes);
+        eng.upload_desc(q, slot, bytes);
+        slate_te_call(te_gemm_batched(eng.device(), stream, dtype, int(opa), int(opb), &alpha, &beta,
+                                      (const te_tile_desc*)slot.dev, (int64_t)batch.descs.size(),
+                                      batch.max_m, batch.max_n));
+        eng.retire_desc(q, slot);
+    }
+    eng.mark_queue(q);
+}
+
+/// op(X)^H expressed as an op on the stored tile; ConjNoTrans is not representable.
+template <typename scalar_t>
+Op conj_trans_of(Op op, bool* ok)
+{
+    *ok = true;
+    if (op == Op::NoTrans) return Op::ConjTrans;
+    if (op == Op::ConjTrans || !is_complex<scalar_t>::value) return Op::NoTrans;
+    *ok = false;
+    return Op::NoTrans;
+}
+template <typename scalar_t>
+Op trans_of(Op op, bool* ok)
+{
+    *ok = true;
+    if (op == Op::NoTrans) return Op::Trans;
+    if (op == Op::Trans || !is_complex<scalar_t>::value) return Op::NoTrans;
+    *ok = false;
+    return Op::NoTrans;
+}
+
+}  // namespace
+
+//------------------------------------------------------------------------------
+template <typename scalar_t>
+void gemm(TargetType<Target::Devices>, scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B,
+          scalar_t beta, Matrix<scalar_t>& C, Layout layout, int priority, int64_t queue_index)
+{
+    slate_assert(layout == Layout::ColMajor);
+    slate_assert(C.mt() > 0 && C.nt() > 0);
+    slate_assert(A.nt() == 1 && B.mt() == 1);
+    slate_assert(A.mt() == C.mt() && B.nt() == C.nt());
+    slate_assert(C.num_devices() > 0);
+    const int device = 0;
+    const int q = (int)queue_index;
+
+    // src/internal/internal_gemm.cc:383-414: if op(C) is not NoTrans, compute the
+    // transposed product on the stored tiles.
+    Op opA = A.op(), opB = B.op();
+    if (C.op() != Op::NoTrans) {
+        if (opA == Op::NoTrans) opA = C.op();
+        else if (A.op() == C.op() || C.is_real) opA = Op::NoTrans;
+        else slate_error("internal::gemm: ConjNoTrans is not supported");
+        if (opB == Op::NoTrans) opB = C.op();
+        else if (B.op() == C.op() || C.is_real) opB = Op::NoTrans;
+        else slate_error("internal::gemm: ConjNoTrans is not supported");
+    }
+    if (C.op() == Op::ConjTrans) {
+        alpha = conj(alpha);
+        beta = conj(beta);
+    }
+
+    // local tiles of C and the A / B tiles they need
+    std::vector<int64_t> rows, cols;
+    std::vector<char> row_used(C.mt(), 0), col_used(C.nt(), 0);
+    std::set<ij_tuple> A_set, B_set, C_set;
+    for (int64_t j = 0; j < C.nt(); ++j)
+        for (int64_t i = 0; i < C.mt(); ++i)
+            if (C.tileIsLocal(i, j)) {
+                row_used[i] = col_used[j] = 1;
+                C_set.insert({i, j});
+            }
+    for (int64_t i = 0; i < C.mt(); ++i)
+        if (row_used[i]) { rows.push_back(i); A_set.insert({i, 0}); }
+    for (int64_t j = 0; j < C.nt(); ++j)
+        if (col_used[j]) { cols.push_back(j); B_set.insert({0, j}); }
+    if (C_set.empty()) return;
+
+    A.tileGetForReading(A_set, device, LayoutConvert(layout), q);
+    B.tileGetForReading(B_set, device, LayoutConvert(layout), q);
+    C.tileGetForWriting(C_set, device, LayoutConvert(layout), q);
+
+    const int64_t k = A.tileNb(0);
+    DescBatch batch;
+    batch.descs.reserve(C_set.size());
+    const bool swap_ab = (C.op() != Op::NoTrans);
+    for (size_t jb = 0; jb < cols.size(); jb += SuperBlock)
+        for (size_t ib = 0; ib < rows.size(); ib += SuperBlock)
+            for (size_t jj = jb; jj < std::min(cols.size(), jb + (size_t)SuperBlock); ++jj)
+                for (size_t ii = ib; ii < std::min(rows.size(), ib + (size_t)SuperBlock); ++ii) {
+                    const int64_t i = rows[ii], j = cols[jj];
+                    if (!C.tileIsLocal(i, j)) continue;
+                    auto Ai = A(i, 0, device);
+                    auto Bj = B(0, j, device);
+                    auto Cij = C(i, j, device);
+                    if (!swap_ab)
+                        batch.add(Ai.data(), Ai.stride(), Bj.data(), Bj.stride(), Cij.data(),
+                                  Cij.stride(), C.tileMb(i), C.tileNb(j), k, TE_TILE_GENERAL);
+                    else   // the stored tile is op(C(i,j)): (n x m) = op'(B_j) op'(A_i)
+                        batch.add(Bj.data(), Bj.stride(), Ai.data(), Ai.stride(), Cij.data(),
+                                  Cij.stride(), C.tileNb(j), C.tileMb(i), k, TE_TILE_GENERAL);
+                }
+    if (swap_ab) std::swap(opA, opB);
+    launch_batch<scalar_t>(batch, q, opA, opB, alpha, beta);
+}
+
+//------------------------------------------------------------------------------
+namespace {
+/// Shared body of herk (conjugate = true) and syrk: lower-logical C, A one block column.
+template <typename scalar_t, typename CMatrix>
+void rank_k_update(bool conjugate, scalar_t alpha, Matrix<scalar_t>& A, scalar_t beta, CMatrix& C,
+                   int queue_index, Layout layout)
+{
+    slate_assert(layout == Layout::ColMajor);
+    slate_assert(C.num_devices() > 0);
+    slate_assert(A.nt() == 1 && A.mt() == C.mt() && C.mt() == C.nt());
+    slate_assert(C.uploLogical() == Uplo::Lower);      // drivers flip upper to lower first
+    const int device = 0;
+    const int q = queue_index;
+
+    // C(i,j) = alpha op(A_i) op(A_j)^{H|T} + beta C(i,j), i >= j.
+    bool ok = true;
+    Op opa = A.op();
+    Op opb = conjugate ? conj_trans_of<scalar_t>(A.op(), &ok) : trans_of<scalar_t>(A.op(), &ok);
+    if (!ok) slate_error("internal::herk/syrk: op(A) mixes Trans and ConjTrans");
+    // stored C tiles are transposed when op(C) != NoTrans:
+    //   P = C(i,j)^{H|T} = alpha op(A_j) op(A_i)^{H|T} + beta P
+    const bool swap_ij = (C.op() != Op::NoTrans);
+    if (swap_ij && is_complex<scalar_t>::value && (C.op() == Op::ConjTrans) != conjugate)
+        slate_error("internal::herk/syrk: op(C) does not match the update");
+    if (swap_ij && conjugate) { alpha = conj(alpha); beta = conj(beta); }
+
+    std::set<ij_tuple> A_set, C_set;
+    for (int64_t j = 0; j < C.nt(); ++j)
+        for (int64_t i = j; i < C.mt(); ++i)
+            if (C.tileIsLocal(i, j)) {
+                C_set.insert({i, j});
+                A_set.insert({i, 0});
+                A_set.insert({j, 0});
+            }
+    if (C_set.empty()) return;
+    A.tileGetForReading(A_set, device, LayoutConvert(layout), q);
+    C.tileGetForWriting(C_set, device, LayoutConvert(layout), q);
+
+    const int64_t k = A.tileNb(0);
+    const int diag_flag = (C.uploPhysical() == Uplo::Lower ? TE_TILE_LOWER : TE_TILE_UPPER)
+                          | (conjugate ? TE_TILE_HERMITIAN : 0);
+    DescBatch batch;
+    batch.descs.reserve(C_set.size());
+    const int64_t nt = C.nt();
+    for (int64_t jb = 0; jb < nt; jb += SuperBlock)
+        for (int64_t ib = jb; ib < nt; ib += SuperBlock)
+            for (int64_t j = jb; j < std::min(nt, jb + SuperBlock); ++j)
+                for (int64_t i = std::max(ib, j); i < std::min(nt, ib + SuperBlock); ++i) {
+                    if (!C.tileIsLocal(i, j)) continue;
+                    auto Ai = A(i, 0, device);
+                    auto Aj = A(j, 0, device);
+                    auto Cij = C(i, j, device);
+                    const int flags = (i == j) ? diag_flag : TE_TILE_GENERAL;
+                    if (!swap_ij)
+                        batch.add(Ai.data(), Ai.stride(), Aj.data(), Aj.stride(), Cij.data(),
+                                  Cij.stride(), C.tileMb(i), C.tileNb(j), k, flags);
+                    else
+                        batch.add(Aj.data(), Aj.stride(), Ai.data(), Ai.stride(), Cij.data(),
+                                  Cij.stride(), C.tileNb(j), C.tileMb(i), k, flags);
+                }
+    launch_batch<scalar_t>(batch, q, opa, opb, alpha, beta);
+}
+}  // namespace
+
+template <typename scalar_t>
+void herk(TargetType<Target::Devices>, real_type<scalar_t> alpha, Matrix<scalar_t>& A,
+          real_type<scalar_t> beta, HermitianMatrix<scalar_t>& C, int priority, int queue_index,
+          Layout layout)
+{
+    rank_k_update<scalar_t>(true, scalar_t(alpha), A, scalar_t(beta), C, queue_index, layout);
+}
+
+template <typename scalar_t>
+void syrk(TargetType<Target::Devices>, scalar_t alpha, Matrix<scalar_t>& A, scalar_t beta,
+          SymmetricMatrix<scalar_t>& C, int priority, int queue_index, Layout layout)
+{
+    rank_k_update<scalar_t>(false, alpha, A, beta, C, queue_index, layout);
+}
+
+//------------------------------------------------------------------------------
+template <typename scalar_t>
+void trsm(TargetType<Target::Devices>, Side side, scalar_t alpha, TriangularMatrix<scalar_t>& A,
+          Matrix<scalar_t>& B, int priority, Layout layout, int64_t queue_index)
+{
+    slate_assert(layout == Layout::ColMajor);
+    slate_assert(B.num_devices() > 0);
+    slate_assert(A.mt() == 1 && A.nt() == 1);
+    slate_assert(side == Side::Left ? A.mt() == B.mt() : A.mt() == B.nt());
+    const int device = 0;
+    const int q = (int)queue_index;
+    Engine& eng = Engine::instance();
+
+    // src/internal/internal_trsm.cc:148-170
+    Uplo uploA = A.uploPhysical();
+    Diag diagA = A.diag();
+    Op opA = A.op();
+    Side sideA = side;
+    if (B.op() != Op::NoTrans) {
+        if (A.is_complex && A.op() != Op::NoTrans && A.op() != B.op())
+            slate_error("internal::trsm: op(A) and op(B) mix Trans and ConjTrans");
+        sideA = (side == Side::Left ? Side::Right : Side::Left);
+        if (A.op() == Op::NoTrans) opA = B.op();
+        else opA = Op::NoTrans;
+        if (B.op() == Op::ConjTrans) alpha = conj(alpha);
+    }
+
+    std::set<ij_tuple> B_set;
+    if (side == Side::Right) {
+        for (int64_t i = 0; i < B.mt(); ++i)
+            if (B.tileIsLocal(i, 0)) B_set.insert({i, 0});
+    }
+    else {
+        for (int64_t j = 0; j < B.nt(); ++j)
+            if (B.tileIsLocal(0, j)) B_set.insert({0, j});
+    }
+    if (B_set.empty()) return;
+
+    {
+        std::set<ij_tuple> one = {{0, 0}};
+        A.tileGetForReading(one, device, LayoutConvert(layout), q);
+    }
+    B.tileGetForWriting(B_set, device, LayoutConvert(layout), q);
+
+    auto A00 = A(0, 0, device);
+    std::vector<te_trsm_desc> descs;
+    int32_t max_m = 0, max_n = 0;
+    for (auto const& ij : B_set) {
+        auto t = B(std::get<0>(ij), std::get<1>(ij), device);
+        t.op(Op::NoTrans);                       // stored extents
+        te_trsm_desc d;
+        d.b = t.data();  d.m = (int32_t)t.mb();  d.n = (int32_t)t.nb();
+        d.ldb = (int32_t)t.stride();  d.reserved = 0;
+        descs.push_back(d);
+        max_m = std::max(max_m, d.m);
+        max_n = std::max(max_n, d.n);
+    }
+    const int na = (int)A.tileMb(0);
+    const int dtype = te_dtype_of<scalar_t>::value;
+    size_t bytes = descs.size() * sizeof(te_trsm_desc);
+    Engine::DescSlot& slot = eng.acquire_desc(q, bytes);
+    std::memcpy(slot.host, descs.data(), bytes);
+    eng.upload_desc(q, slot, bytes);
+    size_t sb = te_trsm_scratch_bytes(dtype, na, (int64_t)descs.size());
+    void* scratch = eng.scratch(q, sb);
+    slate_te_call(te_trsm_batched(eng.device(), eng.compute_stream(q), dtype, int(sideA), int(uploA),
+                                  int(opA), int(diagA), &alpha, A00.data(), (int)A00.stride(), na,
+                                  (const te_trsm_desc*)slot.dev, (int64_t)descs.size(), max_m, max_n,
+                                  scratch, sb));
+    eng.retire_desc(q, slot);
+    eng.mark_queue(q);
+}
+
+//------------------------------------------------------------------------------
+template <typename scalar_t>
+int64_t potrf(TargetType<Target::Devices>, HermitianMatrix<scalar_t>& A, int priority,
+              int64_t queue_index, device_info_int* device_info)
+{
+    slate_assert(A.mt() == 1 && A.nt() == 1);
+    if (!A.tileIsLocal(0, 0)) return 0;
+    const int device = 0;
+    const int q = (int)queue_index;
+    Engine& eng = Engine::instance();
+    std::set<ij_tuple> one = {{0, 0}};
+    A.tileGetForWriting(one, device, LayoutConvert::ColMajor, q);
+    auto A00 = A(0, 0, device);
+    const int dtype = te_dtype_of<scalar_t>::value;
+    int* info_dev = device_info ? device_info : eng.info_slot(4095);
+    size_t sb = te_potrf_scratch_bytes(dtype);
+    // the trsm that follows on the same queue uses the same scratch: stream order keeps them apart
+    void* scratch = eng.scratch(q, sb);
+    slate_te_call(te_potrf_tile(eng.device(), eng.compute_stream(q), dtype,
+                                int(A00.uploPhysical()), (int)A.tileMb(0), A00.data(),
+                                (int)A00.stride(), info_dev, scratch, sb));
+    eng.mark_queue(q);
+    if (device_info) return 0;
+    int info = 0;
+    slate_te_call(te_memcpy_async(&info, info_dev, sizeof(int), TE_COPY_D2H, eng.compute_stream(q)));
+    eng.sync_queue(q);
+    return info;
+}
+
+//------------------------------------------------------------------------------
+void reduce_info(int64_t* info, MPI_Comm comm)
+{
+    if (!comm || comm->size == 1) return;
+    Engine& eng = Engine::instance();
+    int64_t send = (*info == 0) ? std::numeric_limits<int64_t>::max() : *info;
+    int64_t* buf = (int64_t*)eng.scratch(Engine::MaxQueues - 1, sizeof(int64_t));
+    void* stream = eng.comm_stream();
+    slate_te_call(te_memcpy_async(buf, &send, sizeof(send), TE_COPY_H2D, stream));
+    slate_te_call(te_comm_allreduce_i64(comm->nccl, buf, 1, TE_REDUCE_MIN, stream));
+    slate_te_call(te_memcpy_async(&send, buf, sizeof(send), TE_COPY_D2H, stream));
+    eng.sync_comm();
+    *info = (send == std::numeric_limits<int64_t>::max()) ? 0 : send;
+}
+
+//------------------------------------------------------------------------------
+// explicit instantiations (src/internal/internal_gemm.cc:523-636 lists float too; this
+// engine is FP64 / complex-FP64 only)
+#define INSTANTIATE(T)                                                                          \
+    template void gemm<T>(TargetType<Target::Devices>, T, Matrix<T>&, Matrix<T>&, T, Matrix<T>&, \
+                          Layout, int, int64_t);                                                \
+    template void herk<T>(TargetType<Target::Devices>, real_type<T>, Matrix<T>&, real_type<T>,  \
+                          HermitianMatrix<T>&, int, int, Layout);                               \
+    template void syrk<T>(TargetType<Target::Devices>, T, Matrix<T>&, T, SymmetricMatrix<T>&,   \
+                          int, int, Layout);                                                    \
+    template void trsm<T>(TargetType<Target::Devices>, Side, T, TriangularMatrix<T>&,           \
+                          Matrix<T>&, int, Layout, int64_t);                                    \
+    template int64_t potrf<T>(TargetType<Target::Devices>, HermitianMatrix<T>&, int, int64_t,   \
+                              device_info_int*);
+INSTANTIATE(double)
+INSTANTIATE(std::complex<double>)
+
+}  // namespace internal
+}  // namespace slate

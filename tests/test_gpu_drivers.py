@@ -1,0 +1,221 @@
+"""Parity of the host C++ mirror (slate::gemm, slate::potrf, internal::gemm/herk/syrk/
+trsm/potrf on Target::Devices) against the CPU oracle and, when present, the unmodified
+reference (oracle/_ref), on the same matgen inputs.  Mirrors the reference's
+unit_test/test_internal_blas.cc (27 op combinations, ld = m + 1 LAPACK views,
+3*sqrt(k)*eps) and the tester metrics of test/test_gemm.cc / test_posv.cc.  Needs a GPU.
+"""
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+
+pytestmark = pytest.mark.gpu
+EPS = np.finfo(np.float64).eps
+ALPHA, BETA = 3.141592653589793, 2.718281828459045
+
+
+@pytest.fixture(scope="module")
+def sl():
+    from slate_d35_b200 import host
+    host.initialize(0)
+    yield host
+    host.sync()
+
+
+def opn(a, op):
+    return {"N": a, "T": a.T, "C": a.conj().T}[op]
+
+
+@pytest.mark.parametrize("opa", "NTC")
+@pytest.mark.parametrize("opb", "NTC")
+@pytest.mark.parametrize("opc", "NTC")
+def test_internal_gemm_27_ops(sl, opa, opb, opc):
+    """unit_test/test_internal_blas.cc:282-450: m=80, n=64, k=16, nb=16, ld = m+1."""
+    m, n, k, nb = 80, 64, 16, 16
+    ash = (m, k) if opa == "N" else (k, m)
+    bsh = (k, n) if opb == "N" else (n, k)
+    csh = (m, n) if opc == "N" else (n, m)
+    Ab = ol.matgen(1, ash[0] + 1, ash[1], dist=2)
+    Bb = ol.matgen(2, bsh[0] + 1, bsh[1], dist=2)
+    Cb = ol.matgen(3, csh[0] + 1, csh[1], dist=2)
+    A0, B0, C0 = Ab[:ash[0]].copy(), Bb[:bsh[0]].copy(), Cb[:csh[0]].copy()
+    A = sl.Matrix.fromLAPACK(Ab, nb, m=ash[0])
+    B = sl.Matrix.fromLAPACK(Bb, nb, m=bsh[0])
+    Cm = sl.Matrix.fromLAPACK(Cb, nb, m=csh[0])
+    sl.internal_gemm(ALPHA, A, B, BETA, Cm, opa, opb, opc)
+    got = Cm.to_numpy()
+    want = ALPHA * opn(A0, opa) @ opn(B0, opb) + BETA * opn(C0, opc)
+    want = opn(want, opc)              # back to storage orientation
+    assert np.abs(got - want).max() <= 3 * np.sqrt(k) * EPS * max(1.0, np.abs(want).max())
+    assert np.array_equal(Cb[csh[0]:], ol.matgen(3, csh[0] + 1, csh[1], dist=2)[csh[0]:])
+
+
+@pytest.mark.parametrize("kind", ["herk", "syrk"])
+@pytest.mark.parametrize("uplo", "LU")
+@pytest.mark.parametrize("opa", "NT")
+def test_internal_herk_syrk(sl, kind, uplo, opa):
+    """unit_test/test_internal_blas.cc:454-796, vs the oracle's tile herk/syrk."""
+    n, k, nb = 80, 16, 16
+    ash = (n, k) if opa == "N" else (k, n)
+    A0 = ol.matgen(4, *ash, dist=2)
+    C0 = ol.matgen(5, n, n, dist=2)
+    A = sl.Matrix(ash[0], ash[1], nb).from_numpy(A0)
+    cls = sl.HermitianMatrix if kind == "herk" else sl.SymmetricMatrix
+    Cm = cls(uplo, n, nb).from_numpy(C0)
+    if kind == "herk":
+        sl.internal_herk(-1.0, A, 1.0, Cm, opa)
+    else:
+        sl.internal_syrk(-1.0, A, 1.0, Cm, opa)
+    got = Cm.to_numpy()
+    full = -opn(A0, opa) @ opn(A0, opa).T + C0
+    tri = np.tril if uplo == "L" else np.triu
+    assert np.abs(tri(got) - tri(full)).max() <= 3 * np.sqrt(k) * EPS * np.abs(full).max()
+
+
+def test_internal_trsm_and_potrf(sl):
+    nb = 96
+    T0 = ol.matgen(16, nb, nb, dist=2)
+    T0[np.arange(nb), np.arange(nb)] += 20
+    B0 = ol.matgen(17, 250, nb, dist=2)
+    T = sl.TriangularMatrix("L", "N", nb, nb).from_numpy(T0)
+    B = sl.Matrix(250, nb, nb).from_numpy(B0)
+    sl.internal_trsm("R", 1.0, T, B, opa="C")
+    want = B0.copy(order="F")
+    ol.oracle().oracle_tile_dtrsm(ord("R"), ord("L"), ord("C"), ord("N"), 250, nb, 1.0, ol.P(T0), nb,
+                                  ol.P(want), 250)
+    assert np.abs(B.to_numpy() - want).max() <= 50 * EPS * np.sqrt(nb) * np.abs(want).max()
+    H0 = ol.matgen(18, nb, nb)
+    H0[np.arange(nb), np.arange(nb)] += nb
+    H = sl.HermitianMatrix("L", nb, nb).from_numpy(H0)
+    assert sl.internal_potrf(H) == 0
+    want = H0.copy(order="F")
+    assert ol.oracle().oracle_tile_dpotrf(ord("L"), nb, ol.P(want), nb) == 0
+    assert np.abs(np.tril(H.to_numpy()) - np.tril(want)).max() <= 50 * EPS * np.abs(want).max()
+
+
+@pytest.mark.parametrize("origin", ["D", "H"])
+@pytest.mark.parametrize("ops", ["NN", "TN", "NT", "CC"])
+def test_gemm_driver_vs_oracle(sl, origin, ops):
+    """config 1 scaled down: ragged 5x5 tiles, tester alpha/beta (test/test.cc:392-393)."""
+    opa, opb = ops
+    m, n, k, nb = 600, 520, 450, 128
+    ash = (m, k) if opa == "N" else (k, m)
+    bsh = (k, n) if opb == "N" else (n, k)
+    A0, B0, C0 = ol.matgen(1, *ash), ol.matgen(2, *bsh), ol.matgen(3, m, n)
+    if origin == "D":
+        A = sl.Matrix(ash[0], ash[1], nb).generate(1)
+        B = sl.Matrix(bsh[0], bsh[1], nb).generate(2)
+        Cm = sl.Matrix(m, n, nb).generate(3)
+        assert np.array_equal(A.to_numpy(), A0)          # device matgen == host matgen
+    else:
+        Ah, Bh, Ch = A0.copy(order="F"), B0.copy(order="F"), C0.copy(order="F")
+        A, B, Cm = sl.Matrix.fromLAPACK(Ah, nb), sl.Matrix.fromLAPACK(Bh, nb), sl.Matrix.fromLAPACK(Ch, nb)
+    sl.gemm(ALPHA, A, B, BETA, Cm, opa, opb)
+    got = Cm.to_numpy() if origin == "D" else Ch
+    want = C0.copy(order="F")
+    ol.oracle().oracle_dgemm(ord(opa), ord(opb), m, n, k, nb, ALPHA, ol.P(A0), ash[0], ol.P(B0),
+                             bsh[0], BETA, ol.P(want), m)
+    err = np.abs(got - want).max() / np.abs(want).max()
+    assert err <= 3 * np.sqrt(k) * EPS, err
+    if ol.have_ref() and ops == "NN":
+        ref = C0.copy(order="F")
+        ol.ref().ref_dgemm(ord(opa), ord(opb), m, n, k, nb, ALPHA, ol.P(A0), ash[0], ol.P(B0),
+                           bsh[0], BETA, ol.P(ref), m, 1)
+        # north star: relative error against the HostTask path within 50 eps
+        assert np.linalg.norm(got - ref) / np.linalg.norm(ref) <= 50 * EPS
+
+
+def test_gemm_tester_residual(sl):
+    """test/test_gemm.cc:136-158, 196-212: ||C X - (alpha A (B X) + beta C0 X)|| / ||Y|| <= 3 eps."""
+    n, nb, nrhs = 1000, 256, 10
+    A = sl.Matrix(n, n, nb).generate(1)
+    B = sl.Matrix(n, n, nb).generate(2)
+    Cm = sl.Matrix(n, n, nb).generate(3)
+    X = sl.Matrix(n, nrhs, nb).generate(4, dist=2)
+    W = sl.Matrix(n, nrhs, nb)
+    Y = sl.Matrix(n, nrhs, nb)
+    sl.gemm(1.0, B, X, 0.0, W)                 # W = B X
+    sl.gemm(BETA, Cm, X, 0.0, Y)               # Y = beta C0 X
+    sl.gemm(ALPHA, A, W, 1.0, Y)               # Y += alpha A W
+    sl.gemm(ALPHA, A, B, BETA, Cm)
+    Z = sl.Matrix(n, nrhs, nb)
+    sl.gemm(1.0, Cm, X, 0.0, Z)
+    y, z = Y.to_numpy(), Z.to_numpy()
+    assert np.linalg.norm(z - y) / np.linalg.norm(y) <= 3 * EPS
+
+
+@pytest.mark.parametrize("origin", ["D", "H"])
+@pytest.mark.parametrize("uplo", "LU")
+@pytest.mark.parametrize("la", [0, 1, 2])
+def test_potrf_driver_vs_oracle(sl, origin, uplo, la):
+    n, nb = 1000, 128
+    A0 = ol.matgen(7, n, n)
+    A0[np.arange(n), np.arange(n)] += n                   # rand_dominant, test_posv.cc:124
+    if origin == "D":
+        A = sl.HermitianMatrix(uplo, n, nb).from_numpy(A0)
+    else:
+        Ah = A0.copy(order="F")
+        A = sl.HermitianMatrix.fromLAPACK(uplo, Ah, nb)
+    info = sl.potrf(A, lookahead=la)
+    assert info == 0
+    got = A.to_numpy() if origin == "D" else Ah
+    want = A0.copy(order="F")
+    assert ol.oracle().oracle_dpotrf(ord(uplo), n, nb, ol.P(want), n) == 0
+    tri = np.tril if uplo == "L" else np.triu
+    assert np.abs(tri(got) - tri(want)).max() / np.abs(tri(want)).max() <= 50 * EPS
+    # north-star metric, dense evaluation: ||A - L L^H|| / (n ||A||) <= 50 eps
+    F = tri(got)
+    S = np.tril(A0) + np.tril(A0, -1).T if uplo == "L" else np.triu(A0) + np.triu(A0, 1).T
+    R = S - (F @ F.T if uplo == "L" else F.T @ F)
+    assert np.linalg.norm(R) / (n * np.linalg.norm(S)) <= 50 * EPS
+    if origin == "H":
+        other = (lambda x: np.triu(x, 1)) if uplo == "L" else (lambda x: np.tril(x, -1))
+        assert np.array_equal(other(got), other(A0)), "the other triangle is not referenced"
+
+
+def test_potrf_info_not_positive_definite(sl):
+    n, nb = 700, 128
+    A0 = ol.matgen(7, n, n)
+    A0[np.arange(n), np.arange(n)] += n
+    A0[300, 300] = -5.0
+    A = sl.HermitianMatrix("L", n, nb).from_numpy(A0)
+    want = A0.copy(order="F")
+    assert sl.potrf(A) == ol.oracle().oracle_dpotrf(ord("L"), n, nb, ol.P(want), n) == 301
+
+
+def test_potrf_device_generate_and_residual(sl):
+    """device-origin, generated on the GPU, checked with the engine's own residual."""
+    n, nb = 2048, 256
+    A = sl.HermitianMatrix("L", n, nb).generate(11, dominant=True)
+    assert sl.potrf(A) == 0
+    r, a0 = sl.potrf_residual(A, 11, True)
+    assert np.sqrt(r) / (n * np.sqrt(a0)) <= 50 * EPS
+    # and the same number evaluated densely on the host
+    F = np.tril(A.to_numpy())
+    A0 = ol.matgen(11, n, n)
+    A0[np.arange(n), np.arange(n)] += n
+    S = np.tril(A0) + np.tril(A0, -1).T
+    dense = np.linalg.norm(S - F @ F.T)
+    # both are pure rounding noise, accumulated in different orders: same magnitude
+    assert 0.5 * dense <= np.sqrt(r) <= 2.0 * dense
+    assert abs(np.sqrt(a0) - np.linalg.norm(S)) <= 1e-9 * np.linalg.norm(S)
+
+
+def test_host_targets_are_not_built(sl):
+    A = sl.Matrix(64, 64, 32).generate(1)
+    with pytest.raises(sl.SlateError, match="Target::Devices only"):
+        sl.gemm(1.0, A, A, 0.0, A, target="T")
+    H = sl.HermitianMatrix("L", 64, 32).generate(1, dominant=True)
+    with pytest.raises(sl.SlateError, match="Target::Devices only"):
+        sl.potrf(H, target="T")
+
+
+def test_pool_returns_to_level_after_gemm(sl):
+    """workspace blocks taken for host-origin staging all come back (deferred release)."""
+    n, nb = 512, 128
+    Ah, Bh, Ch = ol.matgen(1, n, n), ol.matgen(2, n, n), ol.matgen(3, n, n)
+    A, B, Cm = sl.Matrix.fromLAPACK(Ah, nb), sl.Matrix.fromLAPACK(Bh, nb), sl.Matrix.fromLAPACK(Ch, nb)
+    sl.gemm(1.0, A, B, 1.0, Cm)
+    for M in (A, B, Cm):
+        avail, cap = M.pool_stats()
+        assert avail == cap, (avail, cap)
