@@ -1,0 +1,396 @@
+#!/usr/bin/env python
+"""bench.py -- dgemm FP64 TFLOP/s of slate::gemm (gemmC SUMMA) on the B200 tile engine.
+
+Workload (BASELINE.json configs[1]): slate::gemm<double>, m = n = 65536, nb = 512,
+Target::Devices, device-origin tiles filled by the matgen generator (seeds 1, 2, 3), on a
+p x q grid of 1x1 / 1x2 / 2x2 / 2x4 for 1 / 2 / 4 / 8 GPUs (one rank per GPU, NCCL).
+
+A "step" is one pass of the hot path: one SUMMA block step, i.e. one rank-512 update of
+the whole 65536 x 65536 C (internal::gemm<Devices> = one batched DMMA launch per GPU,
+behind the panel broadcast).  `--steps K` runs slate::gemm with inner dimension k = 512*K,
+so K = 128 (the default) is the complete named configuration; `--warmup W` runs W such
+block steps first in a separate call.  Timing is on the device (CUDA events spanning all
+streams), bracketed by barriers, MAX over ranks.
+
+Extra objects on the JSON line:
+  roofline      dominant kernel (dgemm_tiles_kernel) against the DMMA peak measured in the
+                same process by te_peak_fp64 (MEASURED_PEAKS.json has no FP64 entry)
+  cpu_baseline  the reference's own Target::HostTask path (oracle/_ref) on the host cores,
+                bounded sample, rank 0 at N = 1 only
+  e2e           the same metric through host buffers (Matrix::fromLAPACK / fromScaLAPACK on
+                pinned host arrays): H2D of A, B, C and D2H of C inside the timed region
+  potrf         (unless --no-potrf) dpotrf n = 98304 nb = 512 lookahead 1, info and
+                backward error; secondary metric of BASELINE.json
+
+--impl reference times the reference CPU implementation (oracle/_ref, else the oracle
+port) on the host cores; under torchrun only rank 0 works.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+os.environ.setdefault("OPENBLAS_NUM_THREADS", "1")
+
+N_GEMM = 65536
+NB = 512
+N_POTRF = 98304
+ALPHA, BETA = 3.141592653589793, 2.718281828459045      # test/test.cc:392-393
+GRIDS = {1: (1, 1), 2: (1, 2), 4: (2, 2), 8: (2, 4)}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=128)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--n", type=int, default=N_GEMM, help="override m = n (debug only)")
+    ap.add_argument("--no-potrf", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--potrf-n", type=int, default=N_POTRF)
+    ap.add_argument("--lookahead", type=int, default=1)
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        sm, mx, reasons = [], 0.0, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx = max(mx, float(r[2]))
+                for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                      "sw_power_cap"), r[5:9]):
+                    if val.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        sm.sort()
+        # under load = the upper half of the samples (idle gaps between phases are excluded)
+        load = sm[len(sm) // 2:] if sm else []
+        med = load[len(load) // 2] if load else None
+        return {"sm_mhz": med, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def reference_lib():
+    """(ctypes lib, kind): oracle/_ref when built, else the oracle port."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    if ol.have_ref():
+        return ol, ol.ref(), "reference"
+    return ol, ol.oracle(), "port"
+
+
+def time_reference_gemm(n, k, nb, reps):
+    """reference Target::HostTask slate::gemm (or the oracle port) on host cores -> TFLOP/s"""
+    import numpy as np
+    ol, L, kind = reference_lib()
+    A, B, Cm = ol.matgen(1, n, k), ol.matgen(2, k, n), ol.matgen(3, n, n)
+    best = None
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        if kind == "reference":
+            L.ref_dgemm(ord("N"), ord("N"), n, n, k, nb, ALPHA, ol.P(A), n, ol.P(B), k, BETA,
+                        ol.P(Cm), n, 1)
+        else:
+            L.oracle_dgemm(ord("N"), ord("N"), n, n, k, nb, ALPHA, ol.P(A), n, ol.P(B), k, BETA,
+                           ol.P(Cm), n)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    cores = L.ref_num_threads() if kind == "reference" else L.oracle_num_threads()
+    return 2.0 * n * n * k / best * 1e-12, best, cores, kind
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    os.environ.setdefault("OMP_NUM_THREADS", str(os.cpu_count()))
+    # each step = one block outer product (k = 512) of a bounded m = n sample
+    n_s = 16384 if args.n == N_GEMM else min(args.n, 16384)
+    k = NB * args.steps
+    if args.warmup > 0:
+        time_reference_gemm(n_s, NB * min(args.warmup, 2), NB, 1)
+    tf, secs, cores, kind = time_reference_gemm(n_s, k, NB, 1)
+    line = {
+        "impl": "reference", "metric": "dgemm FP64 TFLOP/s (slate::gemm, gemmC SUMMA)",
+        "value": tf, "unit": "TFLOP/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": secs * 1e3 / args.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"slate::gemm double m=n={N_GEMM} nb={NB} k=nb*steps",
+                   "reference_sample": f"Target::HostTask m=n={n_s} k={k} nb={NB}, 1 rank"},
+        "cpu_baseline": {"value": tf, "unit": "TFLOP/s", "cores": cores, "kind": kind,
+                         "sample": f"m=n={n_s}, k={k}, nb={NB}"},
+        "e2e": {"value": tf, "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------
+def pinned_array(shape, te):
+    """column-major float64 array in pinned host memory (te_host_alloc_pinned)"""
+    import numpy as np
+    nbytes = int(shape[0]) * int(shape[1]) * 8
+    ptr = C.c_void_p()
+    st = te.te_host_alloc_pinned(C.c_size_t(max(nbytes, 8)), C.byref(ptr))
+    if st != 0:
+        raise RuntimeError("te_host_alloc_pinned: " + te.te_last_error().decode())
+    buf = (C.c_double * (nbytes // 8)).from_address(ptr.value)
+    arr = np.frombuffer(buf, dtype=np.float64).reshape(shape[1], shape[0]).T
+    return arr, ptr
+
+
+def local_extent(n, nb, p, r):
+    """rows (or cols) of the 2D block-cyclic local array of process coordinate r of p"""
+    nt = (n + nb - 1) // nb
+    total = 0
+    for t in range(r, nt, p):
+        total += min(nb, n - t * nb)
+    return total
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from slate_d35_b200 import host as sl, lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+    torch.cuda.set_device(local_rank)
+    te = lib()
+    te.te_host_alloc_pinned.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
+    te.te_host_free_pinned.argtypes = [C.c_void_p]
+    te.te_launch_count.restype = C.c_longlong
+
+    nccl_id = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        obj = [sl.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(obj, src=0)
+        nccl_id = obj[0]
+    sl.initialize(local_rank, rank, world, nccl_id)
+    p, q = GRIDS[world]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    n, nb, K, W = args.n, NB, args.steps, args.warmup
+    k = nb * K
+
+    # ---- FP64 tensor (DMMA) peak of this GPU: the roofline denominator -------------------
+    peak = C.c_double()
+    st = te.te_peak_fp64(local_rank, 0, 20000, C.byref(peak))
+    assert st == 0, te.te_last_error()
+    peak_tf = peak.value
+
+    # ---- device-resident run: `value` -----------------------------------------------------
+    A = sl.Matrix(n, k, nb, p, q).generate(1)
+    B = sl.Matrix(k, n, nb, p, q).generate(2)
+    Cm = sl.Matrix(n, n, nb, p, q).generate(3)
+    if W > 0:
+        Aw = sl.Matrix(n, nb * W, nb, p, q).generate(4)
+        Bw = sl.Matrix(nb * W, n, nb, p, q).generate(5)
+        sl.gemm(ALPHA, Aw, Bw, BETA, Cm, lookahead=args.lookahead)
+        Aw.free()
+        Bw.free()
+        Cm.generate(3)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    launches0 = te.te_launch_count()
+    ms = sl.gemm(ALPHA, A, B, BETA, Cm, lookahead=args.lookahead, timed=True)
+    launches = te.te_launch_count() - launches0
+    barrier()
+    ms = max_over_ranks(ms)
+    clocks = sampler.stop() if rank == 0 else None
+    flops = 2.0 * n * n * k
+    value = flops / (ms * 1e-3) * 1e-12
+
+    # the tester's own check on the result (test/test_gemm.cc:136-158, 196-212):
+    # || C X - (alpha A (B X) + beta C0 X) ||_1 / || Y ||_1, X = nrhs columns of kind rand
+    nrhs = 10
+    X = sl.Matrix(n, nrhs, nb, p, q).generate(6)
+    Wm = sl.Matrix(k, nrhs, nb, p, q)
+    Y = sl.Matrix(n, nrhs, nb, p, q)
+    Z = sl.Matrix(n, nrhs, nb, p, q)
+    sl.gemm(1.0, B, X, 0.0, Wm)               # W = B X
+    sl.gemm(ALPHA, A, Wm, 0.0, Y)             # Y = alpha A W
+    sl.gemm(1.0, Cm, X, 0.0, Z)               # Z = C X
+    A.free()
+    B.free()
+    Wm.free()
+    Cm.generate(3)                            # C0 again
+    sl.gemm(BETA, Cm, X, 1.0, Y)              # Y += beta C0 X
+    yh, zh = Y.to_numpy(), Z.to_numpy()       # n x nrhs, this rank's tiles (zeros elsewhere)
+    if world > 1:
+        t = torch.from_numpy(np.stack([yh, zh])).cuda()
+        dist.all_reduce(t)
+        yh, zh = t[0].cpu().numpy(), t[1].cpu().numpy()
+    gemm_error = float(np.abs(zh - yh).sum(axis=0).max() / np.abs(yh).sum(axis=0).max())
+    for M in (X, Y, Z, Cm):
+        M.free()
+
+    # ---- e2e: host buffers, copies inside the timed region -----------------------------
+    e2e = None
+    if not args.no_e2e:
+        myrow, mycol = rank % p, rank // p
+        la_rows, la_k_rows = local_extent(n, nb, p, myrow), local_extent(k, nb, p, myrow)
+        la_cols, la_k_cols = local_extent(n, nb, q, mycol), local_extent(k, nb, q, mycol)
+        Ah, pa = pinned_array((la_rows, la_k_cols), te)
+        Bh, pb = pinned_array((la_k_rows, la_cols), te)
+        Ch, pc = pinned_array((la_rows, la_cols), te)
+        mk = (lambda m_, n_, arr: sl.Matrix.fromScaLAPACK(m_, n_, arr, nb, p, q))
+        Ae, Be, Ce = mk(n, k, Ah), mk(k, n, Bh), mk(n, n, Ch)
+        Ae.generate(1)
+        Be.generate(2)
+        Ce.generate(3)
+        barrier()
+        ms_e = sl.gemm(ALPHA, Ae, Be, BETA, Ce, lookahead=args.lookahead, timed=True)
+        barrier()
+        ms_e = max_over_ranks(ms_e)
+        h2d = 8.0 * (n * k + k * n + n * n)
+        d2h = 8.0 * n * n
+        e2e = {"value": flops / (ms_e * 1e-3) * 1e-12, "unit": "TFLOP/s",
+               "h2d_bytes_per_step": h2d / K, "d2h_bytes_per_step": d2h / K,
+               "ms_per_step": ms_e / K, "host_buffers": "pinned, ScaLAPACK block-cyclic local arrays"}
+        for M in (Ae, Be, Ce):
+            M.free()
+        for ptr in (pa, pb, pc):
+            te.te_host_free_pinned(ptr)
+
+    # ---- dpotrf (secondary metric), N = 1 ------------------------------------------------
+    potrf = None
+    if not args.no_potrf:
+        npo = args.potrf_n
+        H = sl.HermitianMatrix("L", npo, nb, p, q).generate(7, dominant=True)
+        Hw = sl.HermitianMatrix("L", 4 * nb, nb, p, q).generate(8, dominant=True)
+        sl.potrf(Hw, lookahead=args.lookahead)
+        Hw.free()
+        l0 = te.te_launch_count()
+        barrier()
+        info, ms_p = sl.potrf(H, lookahead=args.lookahead, timed=True)
+        barrier()
+        ms_p = max_over_ranks(ms_p)
+        lp = te.te_launch_count() - l0
+        pf = (npo ** 3 / 3.0 + npo ** 2 / 2.0 + npo / 6.0)      # lapack::Gflop<double>::potrf
+        potrf = {"metric": "dpotrf FP64 TFLOP/s (slate::potrf)", "n": npo, "nb": nb,
+                 "lookahead": args.lookahead, "info": int(info), "ms": ms_p,
+                 "value": pf / (ms_p * 1e-3) * 1e-12, "unit": "TFLOP/s",
+                 "frac_of_dmma_peak": pf / (ms_p * 1e-3) * 1e-12 / peak_tf, "gpu_launches": int(lp)}
+        if npo <= 32768:
+            r, a0 = sl.potrf_residual(H, 7, True)
+            if world > 1:
+                t = torch.tensor([r, a0], dtype=torch.float64, device="cuda")
+                dist.all_reduce(t)
+                r, a0 = float(t[0].item()), float(t[1].item())
+            potrf["backward_error"] = (r ** 0.5) / (npo * a0 ** 0.5)
+            potrf["backward_error_bound_50eps"] = 50 * 2.0 ** -52
+        H.free()
+
+    # ---- CPU baseline: the reference's HostTask path on the host cores --------------------
+    cpu = None
+    if not args.no_cpu and rank == 0 and world == 1:
+        os.environ.setdefault("OMP_NUM_THREADS", str(os.cpu_count()))
+        n_s, k_s = (16384, 8192) if n >= 16384 else (n, min(k, 4 * nb))
+        tf_c, secs, cores, kind = time_reference_gemm(n_s, k_s, nb, 1)
+        cpu = {"value": tf_c, "unit": "TFLOP/s", "cores": cores, "kind": kind,
+               "sample": f"Target::HostTask slate::gemm m=n={n_s}, k={k_s}, nb={nb}, "
+                         f"{secs:.1f} s wall, OpenBLAS sequential under OpenMP tasks"}
+
+    if rank == 0:
+        launch_flops = flops / K / world      # one dgemm_tiles_kernel launch per step per GPU
+        traffic = None
+        tfile = os.path.join(ROOT, "profiles", "dgemm_traffic_per_launch.json")
+        if os.path.exists(tfile):
+            try:
+                traffic = json.load(open(tfile)).get("dram_bytes_per_launch")
+            except Exception:
+                traffic = None
+        line = {
+            "metric": "dgemm FP64 TFLOP/s (slate::gemm, gemmC SUMMA)",
+            "value": value, "unit": "TFLOP/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"slate::gemm double m=n={n} nb={nb} k=nb*steps={k} "
+                                   f"Target::Devices origin=Devices lookahead={args.lookahead}",
+                       "grid": f"{p}x{q}", "matgen": "rand seeds 1,2,3",
+                       "l2": "inputs_exceed_l2 (C alone is %.0f GiB)" % (8.0 * n * n / 2 ** 30),
+                       "step": "one SUMMA block step (rank-512 update of C); steps=128 is the full gemm"},
+            "frac_of_fp64_tensor_peak": value / (peak_tf * world),
+            "fp64_dmma_peak_tflops_per_gpu": peak_tf,
+            "gemm_error": gemm_error, "gemm_error_bound_3eps": 3 * 2.0 ** -52,
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "tensor", "achieved": launch_flops / (ms / K * 1e-3) * 1e-12,
+                         "peak": peak_tf, "unit": "TFLOP/s",
+                         "frac": launch_flops / (ms / K * 1e-3) * 1e-12 / peak_tf,
+                         "traffic": traffic, "kernel": "dgemm_tiles_kernel",
+                         "peak_source": "measured in this run by te_peak_fp64 (register-resident "
+                                        "DMMA.8x8x4); MEASURED_PEAKS.json has no FP64 entry"},
+            "e2e": e2e, "cpu_baseline": cpu, "potrf": potrf,
+        }
+        print(json.dumps(line), flush=True)
+    sl.finalize()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

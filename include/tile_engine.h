@@ -54,6 +54,9 @@ const char* te_version(void);
 /* Number of CUDA devices (0 when none; never an error). */
 int te_device_count(void);
 
+/* Kernels this library has launched so far in this process (all devices). */
+long long te_launch_count(void);
+
 /* ------------------------------------------------------------------------
  * Streams, events, copies.  Stand in for blas::Queue and blas::device_memcpy /
  * device_malloc (blaspp/include/blas/device.hh:445-726,

@@ -116,6 +116,7 @@ extern "C" int te_matgen_tile(int device, void* stream, int dtype, int dist, int
     else
         te::matgen_kernel<false><<<grid, 128, 0, (cudaStream_t)stream>>>(
             (double*)A, lda, m, n, ioff, joff, (uint64_t)seed, dist, diag_add);
+    te::count_launch();
     TE_CUDA_CHECK(cudaGetLastError());
     return TE_OK;
 }
@@ -131,6 +132,7 @@ extern "C" int te_tile_add(int device, void* stream, int dtype, int m, int n, do
     dim3 grid((m * esz + 127) / 128, n);
     te::tile_add_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(
         m * esz, n, alpha, (const double*)A, lda * esz, beta, (double*)B, ldb * esz);
+    te::count_launch();
     TE_CUDA_CHECK(cudaGetLastError());
     return TE_OK;
 }
@@ -145,6 +147,7 @@ extern "C" int te_tile_sumsq(int device, void* stream, int dtype, int mask, int 
     dim3 grid((m + 127) / 128 > 8 ? 8 : (m + 127) / 128, n > 64 ? 64 : n);
     te::tile_sumsq_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(
         m, n, (dtype == TE_C64) ? 2 : 1, mask, (const double*)A, lda, accum_dev);
+    te::count_launch();
     TE_CUDA_CHECK(cudaGetLastError());
     return TE_OK;
 }
@@ -159,6 +162,7 @@ extern "C" int te_tile_keep_triangle(int device, void* stream, int dtype, int up
     dim3 grid((m + 127) / 128, n);
     te::tile_keep_triangle_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(
         m, n, (dtype == TE_C64) ? 2 : 1, uplo == TE_UPLO_LOWER ? 1 : 2, (double*)A, lda);
+    te::count_launch();
     TE_CUDA_CHECK(cudaGetLastError());
     return TE_OK;
 }

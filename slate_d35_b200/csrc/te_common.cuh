@@ -20,6 +20,7 @@ void set_last_error(const char* what, const char* detail);
     } while (0)
 
 int num_sms(int device);          // cached cudaDevAttrMultiProcessorCount
+void count_launch(int n = 1);     // kernels launched by this library (te_launch_count)
 int set_device(int device);       // cudaSetDevice with status code
 
 // ---- PTX wrappers -----------------------------------------------------------

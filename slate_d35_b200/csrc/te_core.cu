@@ -1,10 +1,13 @@
 // te_core.cu -- error text, device helpers and identification of the tile engine.
 #include "te_common.cuh"
 #include <string.h>
+#include <atomic>
 
 namespace te {
 
 static thread_local char g_err[512] = "";
+
+long long launches();
 
 void set_last_error(const char* what, const char* detail)
 {
@@ -24,6 +27,10 @@ int num_sms(int device)
     return n;
 }
 
+static std::atomic<long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+long long launches() { return g_launches.load(std::memory_order_relaxed); }
+
 int set_device(int device)
 {
     TE_CUDA_CHECK(cudaSetDevice(device));
@@ -35,6 +42,8 @@ int set_device(int device)
 extern "C" const char* te_last_error(void) { return te::g_err; }
 
 extern "C" const char* te_version(void) { return "tile_engine 0.1 sm_100a"; }
+
+extern "C" long long te_launch_count(void) { return te::launches(); }
 
 extern "C" int te_device_count(void)
 {

@@ -368,6 +368,7 @@ static int launch(int device, cudaStream_t stream, const GemmParams& p)
     const int sms = num_sms(device);
     const int64_t grid = p.total_work < sms ? p.total_work : sms;
     kern<<<(unsigned)grid, NTHREADS, SMEM_BYTES, stream>>>(p);
+    te::count_launch();
     TE_CUDA_CHECK(cudaGetLastError());
     return TE_OK;
 }

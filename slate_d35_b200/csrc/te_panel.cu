@@ -190,6 +190,7 @@ static int potrf_tile(int device, cudaStream_t stream, int dtype, int uplo, int 
         T* Ajj = A + jb + (int64_t)jb * lda;
         potf2_trtri_kernel<T, IB><<<1, PANEL_THREADS, panel_smem_bytes<T>(), stream>>>(
             Ajj, lda, upper, scratch, info, jb, 1, 0, 0, 0, ib);
+        te::count_launch();
         TE_CUDA_CHECK(cudaGetLastError());
         const int rem = n - jb - ib;
         if (rem <= 0) break;
@@ -316,6 +317,7 @@ static int trsm_batched(int device, cudaStream_t stream, int dtype, int side, in
     potf2_trtri_kernel<T, IB><<<nblk, PANEL_THREADS, panel_smem_bytes<T>(), stream>>>(
         const_cast<T*>(A), lda, uplo == TE_UPLO_UPPER, inv, nullptr, 0, 0,
         diag == TE_DIAG_UNIT, (int64_t)IB + (int64_t)IB * lda, (int64_t)IB * IB, na);
+    te::count_launch();
     TE_CUDA_CHECK(cudaGetLastError());
 
     // 2. descriptors of every step
@@ -327,6 +329,7 @@ static int trsm_batched(int device, cudaStream_t stream, int dtype, int side, in
     p.eff_lower = ((uplo == TE_UPLO_LOWER) == (opa == TE_OP_N));
     const int64_t total = (int64_t)nblk * count;
     trsm_build_descs_kernel<<<(unsigned)((total + 127) / 128), 128, 0, stream>>>(p);
+    te::count_launch();
     TE_CUDA_CHECK(cudaGetLastError());
 
     // 3. block substitution, two GEMM launches per diagonal block

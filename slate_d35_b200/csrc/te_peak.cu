@@ -51,6 +51,7 @@ static void launch_peak(int kind, int grid, int threads, int iters, double* sink
         peak_dmma_kernel<CHAINS><<<grid, threads>>>(iters, 0.25, sink);
     else
         peak_dfma_kernel<CHAINS><<<grid, threads>>>(iters, 0.25, sink);
+    te::count_launch();
 }
 
 }  // namespace te

@@ -122,7 +122,8 @@ class _Base:
         ptr, ld = None, 0
         if host_array is not None:
             assert host_array.flags.f_contiguous and host_array.dtype == self.dtype
-            assert host_array.shape[0] >= m and host_array.shape[1] == n
+            if origin != "S":
+                assert host_array.shape[0] >= m and host_array.shape[1] == n
             ptr, ld = host_array.ctypes.data, host_array.shape[0]
         _check(hostlib().sb_matrix_create(_dtype_code(dtype), self.kind, ord(uplo), ord(diag), m, n,
                                           nb, p, q, ord(origin), ptr, ld, C.byref(h)))
@@ -177,6 +178,13 @@ class Matrix(_Base):
         """View of the first m rows (default all) of the column-major array a (ld = a.shape[0])."""
         return cls(a.shape[0] if m is None else m, a.shape[1], nb, p, q, a.dtype, origin="H",
                    host_array=a)
+
+
+    @classmethod
+    def fromScaLAPACK(cls, m, n, local, nb, p, q):
+        """`local` is this rank's 2D block-cyclic local array (column-major, ld = local.shape[0]),
+        as ScaLAPACK lays it out (include/slate/Matrix.hh:486-520)."""
+        return cls(m, n, nb, p, q, local.dtype, origin="S", host_array=local)
 
 
 class HermitianMatrix(_Base):

@@ -87,7 +87,9 @@ void create(Handle* h, int kind, int uplo, int diag, int64_t m, int64_t n, int64
     if (p * q == 1 && comm->size > 1) comm = MPI_COMM_SELF;
     switch (kind) {
         case General: {
-            auto M = host ? std::make_shared<Matrix<T>>(Matrix<T>::fromLAPACK(m, n, host, ld, nb, p, q, comm))
+            auto M = host ? std::make_shared<Matrix<T>>(
+                                origin == 'S' ? Matrix<T>::fromScaLAPACK(m, n, host, ld, nb, p, q, comm)
+                                              : Matrix<T>::fromLAPACK(m, n, host, ld, nb, p, q, comm))
                           : std::make_shared<Matrix<T>>(m, n, nb, p, q, comm);
             if (!host) M->insertLocalTiles(org);
             h->obj = M;
