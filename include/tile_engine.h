@@ -206,6 +206,36 @@ int te_trsm_batched(int device, void* stream, int dtype, int side, int uplo, int
                     const te_trsm_desc* b_desc, int64_t count, int32_t max_m, int32_t max_n,
                     void* scratch, size_t scratch_bytes);
 
+/* Allocation-free variant of te_trsm_batched.  It has no counterpart in the
+ * reference (blas::batch::trsm takes no workspace argument; cuBLAS allocates
+ * what it needs behind the call).
+ *
+ * Who needs it: callers that cannot give the engine device scratch and cannot
+ * allocate any at this point -- a solver whose tile pool has already claimed
+ * all the HBM it may use, or a panel step that must not risk cudaMalloc
+ * stalling the device.  The scratch is a fixed 768 KiB block inside the
+ * library image on every GPU that loads it (held until the process exits), so
+ * the call makes no cudaMalloc / cudaFree and uses no allocating library
+ * routine.  Arguments and results are those of te_trsm_batched without the
+ * scratch pair.
+ *
+ * Limits: na <= TE_TRSM_STATIC_MAX_NA and count <= TE_TRSM_STATIC_MAX_COUNT;
+ * anything larger returns TE_ERR_LIMIT with the limits in te_last_error().
+ * The first call on a device looks up the block's device address
+ * (cudaGetSymbolAddress) and sets kernel attributes; make that first call
+ * before starting any stream capture on that device.
+ * All calls on a device share the one block: two calls whose work can overlap
+ * on the GPU (different streams with no ordering between them) race and give
+ * wrong results -- keep them on one stream or order them with events.  The
+ * block keeps the previous call's contents; nothing in it needs to start at
+ * zero because each call overwrites every part before reading it. */
+#define TE_TRSM_STATIC_MAX_NA    512
+#define TE_TRSM_STATIC_MAX_COUNT 256
+int te_trsm_batched_static(int device, void* stream, int dtype, int side, int uplo, int opa,
+                           int diag, const void* alpha, const void* A, int lda, int na,
+                           const te_trsm_desc* b_desc, int64_t count, int32_t max_m,
+                           int32_t max_n);
+
 /* ------------------------------------------------------------------------
  * Tile broadcasts between the box's GPUs over NCCL (one rank per GPU).
  *

@@ -64,6 +64,8 @@ def lib():
     L.te_trsm_scratch_bytes.argtypes = [C.c_int, C.c_int, i64]
     L.te_trsm_batched.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp,
                                   C.c_int, C.c_int, vp, i64, i32, i32, vp, sz]
+    L.te_trsm_batched_static.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                         vp, vp, C.c_int, C.c_int, vp, i64, i32, i32]
     L.te_matgen_tile.argtypes = [C.c_int, vp, C.c_int, C.c_int, i64, C.c_int, C.c_int, i64, i64,
                                  vp, i64, C.c_double]
     L.te_tile_add.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_double, vp, i64,

@@ -18,6 +18,7 @@
 // block, which holds because IB <= 128).  `info` stays on the device: nothing
 // here synchronises with the host.
 #include "te_common.cuh"
+#include <mutex>
 
 namespace te {
 
@@ -411,4 +412,84 @@ extern "C" int te_trsm_batched(int device, void* stream, int dtype, int side, in
                                         alpha, (const te::zd*)A, lda, na, b_desc, count, max_m,
                                         max_n, scratch, scratch_bytes);
     return TE_ERR_ARG;
+}
+
+// ---------------------- allocation-free batched trsm ---------------------------
+// Same computation as te_trsm_batched, for callers that have no device memory to
+// hand over as scratch and are not in a position to obtain any: a solver that has
+// already committed its whole HBM budget to the tile pool, or a panel step on the
+// critical path that must not run into cudaMalloc (which can stall every stream of
+// the device while it runs).  The scratch lives in the library image instead.
+//
+// te_trsm_static_scratch is that storage: one fixed block per GPU that loads the
+// library, held until the process exits.  In host code the symbol below is only a
+// handle, not something a kernel may dereference; the device address is looked up
+// once per device with cudaGetSymbolAddress and that pointer is what the kernels get.
+#define TE_TRSM_STATIC_SCRATCH_BYTES (768u * 1024u)
+static __device__ __align__(256) unsigned char te_trsm_static_scratch[TE_TRSM_STATIC_SCRATCH_BYTES];
+
+namespace te {
+
+static std::mutex g_static_scratch_mu;
+static void* g_static_scratch_ptr[64] = {};
+
+// Device address of te_trsm_static_scratch on `device` (which must be current).
+static int static_scratch_address(int device, void** out)
+{
+    if (device < 0 || device >= 64) return TE_ERR_ARG;
+    std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+    if (!g_static_scratch_ptr[device]) {
+        void* ptr = nullptr;
+        TE_CUDA_CHECK(cudaGetSymbolAddress((void**)&ptr, te_trsm_static_scratch));
+        g_static_scratch_ptr[device] = ptr;
+    }
+    *out = g_static_scratch_ptr[device];
+    return TE_OK;
+}
+
+}  // namespace te
+
+extern "C" int te_trsm_batched_static(int device, void* stream, int dtype, int side, int uplo,
+                                      int opa, int diag, const void* alpha, const void* A, int lda,
+                                      int na, const te_trsm_desc* b_desc, int64_t count,
+                                      int32_t max_m, int32_t max_n)
+{
+    if (!alpha || !A || na < 0 || count < 0 || (count > 0 && !b_desc) ||
+        (dtype != TE_F64 && dtype != TE_C64) ||
+        (side != TE_SIDE_LEFT && side != TE_SIDE_RIGHT) ||
+        (uplo != TE_UPLO_LOWER && uplo != TE_UPLO_UPPER) ||
+        (opa != TE_OP_N && opa != TE_OP_T && opa != TE_OP_C) ||
+        (diag != TE_DIAG_NONUNIT && diag != TE_DIAG_UNIT))
+        return TE_ERR_ARG;
+    if (na > TE_TRSM_STATIC_MAX_NA || count > TE_TRSM_STATIC_MAX_COUNT) {
+        char msg[200];
+        snprintf(msg, sizeof(msg),
+                 "na = %d, count = %lld exceed the built-in scratch (na <= %d, count <= %d); "
+                 "use te_trsm_batched with caller scratch",
+                 na, (long long)count, TE_TRSM_STATIC_MAX_NA, TE_TRSM_STATIC_MAX_COUNT);
+        te::set_last_error("te_trsm_batched_static", msg);
+        return TE_ERR_LIMIT;
+    }
+    if (count == 0 || na == 0 || max_m == 0 || max_n == 0)
+        return TE_OK;
+    int st = te::set_device(device);
+    if (st != TE_OK) return st;
+    void* scratch = nullptr;
+    st = te::static_scratch_address(device, &scratch);
+    if (st != TE_OK) return st;
+    const size_t need = te_trsm_scratch_bytes(dtype, na, count);
+    if (need > TE_TRSM_STATIC_SCRATCH_BYTES) {      // cannot happen within the two limits
+        te::set_last_error("te_trsm_batched_static", "internal: limits exceed the static block");
+        return TE_ERR_LIMIT;
+    }
+    // Every byte of the block that this call reads (the inverted diagonal blocks and the
+    // per-step descriptors) is written by this call first, so whatever an earlier call
+    // left behind needs no clearing.
+    if (dtype == TE_F64)
+        return te::trsm_batched<double>(device, (cudaStream_t)stream, dtype, side, uplo, opa, diag,
+                                        alpha, (const double*)A, lda, na, b_desc, count, max_m,
+                                        max_n, scratch, TE_TRSM_STATIC_SCRATCH_BYTES);
+    return te::trsm_batched<te::zd>(device, (cudaStream_t)stream, dtype, side, uplo, opa, diag,
+                                    alpha, (const te::zd*)A, lda, na, b_desc, count, max_m,
+                                    max_n, scratch, TE_TRSM_STATIC_SCRATCH_BYTES);
 }
