@@ -310,41 +310,76 @@ dgemm_tiles_kernel(const __grid_constant__ GemmParams p)
             const bool lower = (it.flags & TE_TILE_LOWER) != 0;
             const bool upper = (it.flags & TE_TILE_UPPER) != 0;
             double* cblk = it.c + (int64_t)it.n0 * it.ldc + it.m0;
+            const bool interior = (it.m >= wm + 64) && (it.n >= wn + 32) && !lower && !upper && it.c16;
+            if (interior) {
+                // Whole 64x32 warp tile inside the block, 16-byte aligned: branch-free, with all
+                // loads of a half (16 x 16 bytes per lane) in flight before the first use, so the
+                // C read costs one memory round trip instead of one per fragment.
+                double* c0 = cblk + (int64_t)(wn + g) * it.ldc + wm + 2 * t;
+                const int64_t cstep = (int64_t)8 * it.ldc;
 #pragma unroll
-            for (int in = 0; in < 4; ++in) {
-                const int col = wn + in * 8 + g;
-                if (col >= it.n)
-                    continue;
-                double* ccol = cblk + (int64_t)col * it.ldc;
-                const int gcol = it.n0 + col;          // column inside the tile
+                for (int h = 0; h < 2; ++h) {
+                    double2 old[2][8];
+                    if (beta != 0.0) {
 #pragma unroll
-                for (int im = 0; im < 8; ++im) {
-                    const int row = wm + im * 8 + 2 * t;
-                    if (row >= it.m)
-                        continue;
-                    const int grow = it.m0 + row;
-                    bool ok0 = true, ok1 = (row + 1 < it.m);
-                    if (lower) { ok0 = ok0 && (grow >= gcol); ok1 = ok1 && (grow + 1 >= gcol); }
-                    if (upper) { ok0 = ok0 && (grow <= gcol); ok1 = ok1 && (grow + 1 <= gcol); }
-                    double v0 = alpha * acc[in][im][0];
-                    double v1 = alpha * acc[in][im][1];
-                    double* dst = ccol + row;
-                    if (ok0 && ok1 && it.c16) {
-                        if (beta != 0.0) {
-                            const double2 old = *reinterpret_cast<const double2*>(dst);
-                            v0 += beta * old.x;
-                            v1 += beta * old.y;
-                        }
-                        *reinterpret_cast<double2*>(dst) = make_double2(v0, v1);
+                        for (int i2 = 0; i2 < 2; ++i2)
+#pragma unroll
+                            for (int im = 0; im < 8; ++im)
+                                old[i2][im] = *reinterpret_cast<const double2*>(
+                                    c0 + (2 * h + i2) * cstep + im * 8);
                     }
-                    else {
-                        if (ok0) {
-                            if (beta != 0.0) v0 += beta * dst[0];
-                            dst[0] = v0;
+#pragma unroll
+                    for (int i2 = 0; i2 < 2; ++i2)
+#pragma unroll
+                        for (int im = 0; im < 8; ++im) {
+                            double v0 = alpha * acc[2 * h + i2][im][0];
+                            double v1 = alpha * acc[2 * h + i2][im][1];
+                            if (beta != 0.0) {
+                                v0 += beta * old[i2][im].x;
+                                v1 += beta * old[i2][im].y;
+                            }
+                            *reinterpret_cast<double2*>(c0 + (2 * h + i2) * cstep + im * 8) =
+                                make_double2(v0, v1);
                         }
-                        if (ok1) {
-                            if (beta != 0.0) v1 += beta * dst[1];
-                            dst[1] = v1;
+                }
+            }
+            else {
+#pragma unroll
+                for (int in = 0; in < 4; ++in) {
+                    const int col = wn + in * 8 + g;
+                    if (col >= it.n)
+                        continue;
+                    double* ccol = cblk + (int64_t)col * it.ldc;
+                    const int gcol = it.n0 + col;          // column inside the tile
+#pragma unroll
+                    for (int im = 0; im < 8; ++im) {
+                        const int row = wm + im * 8 + 2 * t;
+                        if (row >= it.m)
+                            continue;
+                        const int grow = it.m0 + row;
+                        bool ok0 = true, ok1 = (row + 1 < it.m);
+                        if (lower) { ok0 = ok0 && (grow >= gcol); ok1 = ok1 && (grow + 1 >= gcol); }
+                        if (upper) { ok0 = ok0 && (grow <= gcol); ok1 = ok1 && (grow + 1 <= gcol); }
+                        double v0 = alpha * acc[in][im][0];
+                        double v1 = alpha * acc[in][im][1];
+                        double* dst = ccol + row;
+                        if (ok0 && ok1 && it.c16) {
+                            if (beta != 0.0) {
+                                const double2 old = *reinterpret_cast<const double2*>(dst);
+                                v0 += beta * old.x;
+                                v1 += beta * old.y;
+                            }
+                            *reinterpret_cast<double2*>(dst) = make_double2(v0, v1);
+                        }
+                        else {
+                            if (ok0) {
+                                if (beta != 0.0) v0 += beta * dst[0];
+                                dst[0] = v0;
+                            }
+                            if (ok1) {
+                                if (beta != 0.0) v1 += beta * dst[1];
+                                dst[1] = v1;
+                            }
                         }
                     }
                 }
