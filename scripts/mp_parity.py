@@ -1,0 +1,111 @@
+"""Multi-rank parity: slate::gemm and slate::potrf on a p x q grid (one rank per GPU, NCCL
+tile broadcasts) against the CPU oracle.  Run under torchrun:
+
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+      --master-port 29511 scripts/mp_parity.py
+
+Every rank gathers its own tiles (zeros elsewhere); an all-reduce sum assembles the matrix.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import oracle_lib as ol  # noqa: E402
+from slate_d35_b200 import host as sl  # noqa: E402
+
+GRIDS = {1: [(1, 1)], 2: [(1, 2), (2, 1)], 4: [(2, 2), (1, 4)], 8: [(2, 4), (4, 2)]}
+EPS = np.finfo(np.float64).eps
+
+
+def assemble(M):
+    t = torch.from_numpy(np.ascontiguousarray(M.to_numpy())).cuda()
+    dist.all_reduce(t)
+    return np.asfortranarray(t.cpu().numpy())
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    lr = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(lr)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+    obj = [sl.nccl_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(obj, src=0)
+    sl.initialize(lr, rank, world, obj[0])
+    fails = 0
+    for (p, q) in GRIDS[world]:
+        for la in (0, 1, 2):
+            # ---- gemm, ragged tiles, tester alpha/beta ----
+            m, n, k, nb = 1500, 1300, 1100, 256
+            alpha, beta = 3.141592653589793, 2.718281828459045
+            A = sl.Matrix(m, k, nb, p, q).generate(1)
+            B = sl.Matrix(k, n, nb, p, q).generate(2)
+            Cm = sl.Matrix(m, n, nb, p, q).generate(3)
+            sl.gemm(alpha, A, B, beta, Cm, lookahead=la)
+            got = assemble(Cm)
+            if rank == 0:
+                A0, B0, want = ol.matgen(1, m, k), ol.matgen(2, k, n), ol.matgen(3, m, n)
+                ol.oracle().oracle_dgemm(ord("N"), ord("N"), m, n, k, nb, alpha, ol.P(A0), m, ol.P(B0),
+                                         k, beta, ol.P(want), m)
+                err = np.abs(got - want).max() / np.abs(want).max()
+                ok = err <= 3 * np.sqrt(k) * EPS
+                fails += (not ok)
+                print(f"gemm  {p}x{q} la={la}: err {err:.2e} {'ok' if ok else 'FAIL'}", flush=True)
+            for M in (A, B, Cm):
+                M.free()
+            # ---- potrf ----
+            for uplo in "LU":
+                n, nb = 1800, 256
+                H = sl.HermitianMatrix(uplo, n, nb, p, q).generate(7, dominant=True)
+                info = sl.potrf(H, lookahead=la)
+                got = assemble(H)
+                if uplo == "L":
+                    r, a0 = sl.potrf_residual(H, 7, True)
+                    t = torch.tensor([r, a0], dtype=torch.float64, device="cuda")
+                    dist.all_reduce(t)
+                    berr = float(t[0].sqrt() / (n * t[1].sqrt()))
+                else:
+                    berr = 0.0
+                if rank == 0:
+                    want = ol.matgen(7, n, n)
+                    want[np.arange(n), np.arange(n)] += n
+                    assert ol.oracle().oracle_dpotrf(ord(uplo), n, nb, ol.P(want), n) == 0
+                    tri = np.tril if uplo == "L" else np.triu
+                    err = np.abs(tri(got) - tri(want)).max() / np.abs(tri(want)).max()
+                    ok = info == 0 and err <= 50 * EPS and berr <= 50 * EPS
+                    fails += (not ok)
+                    print(f"potrf {p}x{q} la={la} {uplo}: info {info} err {err:.2e} backward {berr:.2e} "
+                          f"{'ok' if ok else 'FAIL'}", flush=True)
+                H.free()
+    # info must be the same on every rank
+    n, nb = 1200, 256
+    p, q = GRIDS[world][0]
+    A0 = ol.matgen(7, n, n)
+    A0[np.arange(n), np.arange(n)] += n
+    A0[700, 700] = -3.0
+    H = sl.HermitianMatrix("L", n, nb, p, q).from_numpy(A0)
+    info = sl.potrf(H)
+    t = torch.tensor([info], dtype=torch.int64, device="cuda")
+    lo, hi = t.clone(), t.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        ok = int(lo.item()) == int(hi.item()) == 701
+        fails += (not ok)
+        print(f"potrf info on all ranks: {int(lo.item())}..{int(hi.item())} {'ok' if ok else 'FAIL'}", flush=True)
+    H.free()
+    sl.finalize()
+    dist.barrier()
+    dist.destroy_process_group()
+    if rank == 0:
+        print("MP_PARITY", "PASS" if fails == 0 else f"FAIL ({fails})", flush=True)
+    sys.exit(1 if fails else 0)
+
+
+if __name__ == "__main__":
+    main()
