@@ -280,7 +280,7 @@ def main():
     sl.gemm(BETA, Cm, X, 1.0, Y)              # Y += beta C0 X
     yh, zh = Y.to_numpy(), Z.to_numpy()       # n x nrhs, this rank's tiles (zeros elsewhere)
     if world > 1:
-        t = torch.from_numpy(np.stack([yh, zh])).cuda()
+        t = torch.from_numpy(np.ascontiguousarray(np.stack([yh, zh]))).cuda()
         dist.all_reduce(t)
         yh, zh = t[0].cpu().numpy(), t[1].cpu().numpy()
     gemm_error = float(np.abs(zh - yh).sum(axis=0).max() / np.abs(yh).sum(axis=0).max())

@@ -1,6 +1,6 @@
 // te_gemm.cu -- batched FP64 tile update  C_i = alpha op(A_i) op(B_i) + beta C_i
 //
-// One persistent launch per block outer product per device.  Replaces the
+// One launch per block outer product per device.  Replaces the
 // cublasDgemmBatched / cublasDsyrk calls behind SLATE's
 // internal::gemm/herk/syrk<Target::Devices>
 // (reference: src/internal/internal_gemm.cc:355-518, internal_herk.cc:351-535,
@@ -9,16 +9,22 @@
 // Design (B200, sm_100a)
 //   * tcgen05/TMEM has no FP64 kind, so the FP64 tensor path is the
 //     warp-synchronous DMMA.8x8x4 (mma.sync.m8n8k4.f64).
-//   * CTA tile 128x128, 8 warps, warp tile 64(m) x 32(n): 32 accumulator
-//     fragments (128 registers) per thread, 12 LDS.64 per 32 DMMA.
+//   * CTA tile 128x128, 8 consumer warps with warp tile 64(m) x 32(n): 32
+//     accumulator fragments (128 registers) per thread, 12 LDS.64 per 32 DMMA;
+//     4 producer warps; setmaxnreg moves registers from producers to consumers.
 //   * operands staged GMEM -> SMEM by 16-byte cp.async (.cg, L2 only) through
-//     a 4-stage ring of K=16 slices; +4 padding per row makes every
-//     64-bit fragment load bank-conflict free for both storage orders.
-//   * persistent CTAs (one per SM) walk a flat list of (tile, 128x128 block)
-//     work items in the order the host laid the descriptors out (the host
-//     orders them for L2 reuse of the A/B panels); the cp.async ring runs
-//     ACROSS work items, so the next block's first slices are in flight while
-//     the current block's epilogue reads/writes C.
+//     a 5-stage ring of K=16 slices guarded by mbarriers; +4 padding per row
+//     makes every 64-bit fragment load bank-conflict free for both storage
+//     orders.
+//   * the flat list of (tile, 128x128 block) work items, in the order the host
+//     laid the descriptors out (ordered for L2 reuse of the A/B panels), is cut
+//     into runs of up to 8 consecutive items per CTA (one CTA per SM at a time,
+//     ~0.5 ms each).  Inside a run the cp.async ring runs ACROSS items, so the
+//     next block's first slices are in flight while the current block's epilogue
+//     reads/writes C.  Short-lived CTAs let the block scheduler balance the load
+//     and let higher-priority streams (NCCL broadcasts, the Cholesky panel) take
+//     SMs as CTAs retire; a persistent grid with fixed shares doubled the kernel
+//     time whenever an NCCL kernel held a few SMs (measured on 2 GPUs).
 //   * ragged edges (m, n, k not multiples of the tile) are zero-filled by
 //     cp.async src-size and masked in the epilogue; odd leading dimensions /
 //     8-byte aligned tiles fall back to 8-byte cp.async per element.
@@ -26,6 +32,7 @@
 //     column (the MMA is issued on C^T), so C is read/written as 16-byte
 //     vectors forming 64-byte column segments per quad.
 #include "te_common.cuh"
+#include <stdlib.h>
 
 namespace te {
 
@@ -48,6 +55,7 @@ constexpr int SMEM_BYTES = STAGES * 2 * SLICE * (int)sizeof(double) + 2 * STAGES
 struct GemmParams {
     const te_tile_desc* desc;      // device array (batched mode)
     int64_t total_work;            // count * blocks_per_tile
+    int32_t items_per_cta;         // consecutive work items handled by one CTA
     int32_t nbm, nbn;              // 128-blocks per tile in m and n
     double alpha, beta;
     int32_t inline_count;          // > 0: use inl[] instead of desc
@@ -102,11 +110,15 @@ __device__ __forceinline__ bool decode(const GemmParams& p, int64_t w, Item& it)
     return true;
 }
 
-// Walks the work list of this CTA: w = blockIdx.x, += gridDim.x, skipping
-// blocks that fall outside their (ragged / triangular) tile.
+// Walks the work list of this CTA: the items_per_cta consecutive items starting at
+// blockIdx.x * items_per_cta, skipping blocks that fall outside their (ragged /
+// triangular) tile.  CTAs are short-lived on purpose (a few hundred microseconds): the
+// hardware block scheduler then balances the load by itself and lets kernels on
+// higher-priority streams (NCCL broadcasts, the Cholesky panel) take SMs as CTAs retire,
+// which a grid of persistent CTAs with fixed shares would block.
 template <bool INL>
 struct Walker {
-    int64_t w;
+    int64_t w, w_end;
     int nk;        // K slices of the current item
     bool valid;
     Item it;
@@ -114,23 +126,25 @@ struct Walker {
     __device__ __forceinline__ void seek(const GemmParams& p)
     {
         valid = false;
-        while (w < p.total_work) {
+        while (w < w_end) {
             if (decode<INL>(p, w, it)) {
                 valid = true;
                 nk = (it.k + KC - 1) / KC;
                 return;
             }
-            w += gridDim.x;
+            ++w;
         }
     }
     __device__ __forceinline__ void start(const GemmParams& p)
     {
-        w = blockIdx.x;
+        w = (int64_t)blockIdx.x * p.items_per_cta;
+        w_end = w + p.items_per_cta;
+        if (w_end > p.total_work) w_end = p.total_work;
         seek(p);
     }
     __device__ __forceinline__ void next_item(const GemmParams& p)
     {
-        w += gridDim.x;
+        ++w;
         seek(p);
     }
 };
@@ -400,12 +414,28 @@ static int launch(int device, cudaStream_t stream, const GemmParams& p)
                                            SMEM_BYTES));
         configured[device] = true;
     }
-    const int sms = num_sms(device);
-    const int64_t grid = p.total_work < sms ? p.total_work : sms;
+    const int64_t grid = (p.total_work + p.items_per_cta - 1) / p.items_per_cta;
     kern<<<(unsigned)grid, NTHREADS, SMEM_BYTES, stream>>>(p);
     te::count_launch();
     TE_CUDA_CHECK(cudaGetLastError());
     return TE_OK;
+}
+
+// Up to 8 consecutive 128x128 blocks per CTA (about 0.5 ms at k = 512) once there are
+// enough blocks for several waves; fewer when the launch is small, so that it still
+// spreads over all SMs.
+static int items_per_cta(int device, int64_t total_work)
+{
+    static int cap = -1;
+    if (cap < 0) {
+        const char* e = getenv("TE_ITEMS_PER_CTA");
+        cap = (e && atoi(e) > 0) ? atoi(e) : 8;
+    }
+    const int64_t sms = num_sms(device);
+    int64_t g = total_work / (4 * sms);
+    if (g < 1) g = 1;
+    if (g > cap) g = cap;
+    return (int)g;
 }
 
 template <bool INL>
@@ -428,6 +458,7 @@ int dgemm_batched(int device, cudaStream_t stream, int opa, int opb, double alph
     p.nbm = (max_m + BM - 1) / BM;
     p.nbn = (max_n + BN - 1) / BN;
     p.total_work = count * p.nbm * p.nbn;
+    p.items_per_cta = items_per_cta(device, p.total_work);
     p.alpha = alpha;
     p.beta = beta;
     p.inline_count = 0;
@@ -448,6 +479,7 @@ int dgemm_inline(int device, cudaStream_t stream, int opa, int opb, double alpha
     p.nbm = (max_m + BM - 1) / BM;
     p.nbn = (max_n + BN - 1) / BN;
     p.total_work = (int64_t)count * p.nbm * p.nbn;
+    p.items_per_cta = items_per_cta(device, p.total_work);
     p.alpha = alpha;
     p.beta = beta;
     p.inline_count = count;

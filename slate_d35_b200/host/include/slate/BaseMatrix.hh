@@ -185,7 +185,10 @@ public:
             slate_assert(node.dev);
             node.dev_state = MOSI::Modified;
             if (node.host) node.host_state = MOSI::Invalid;
-            if (queue >= 0) node.write_queue = queue;
+            if (queue >= 0) {
+                node.write_queue = queue;
+                node.write_seq = Engine::instance().next_queue_seq(queue);
+            }
         }
     }
 
@@ -402,7 +405,8 @@ protected:
             Engine::instance().mark_comm();
             device_copies_pending_ = false;
         }
-        if (queue >= 0) Engine::instance().queue_wait_comm(queue);
+        if (queue >= 0) Engine::instance().queue_wait_comm_seq(queue, needed_comm_seq_);
+        needed_comm_seq_ = 0;
     }
 
     int64_t ioffset_, joffset_, mt_, nt_;
@@ -413,6 +417,7 @@ protected:
     std::shared_ptr<MatrixStorage<scalar_t>> storage_;
     bool host_copies_pending_ = false;
     bool device_copies_pending_ = false;
+    uint64_t needed_comm_seq_ = 0;
 
     template <typename T> friend class BaseMatrix;
 };
@@ -427,8 +432,8 @@ void BaseMatrix<scalar_t>::tileGet(int64_t i, int64_t j, int device, bool modify
         if (!(node.host && node.host_state != MOSI::Invalid)) {
             slate_assert(node.dev && node.dev_state != MOSI::Invalid);
             if (!node.host) storage_->tileInsert(globalIndex(i, j), HostNum, TileKind::Workspace);
-            // device -> host: after the queue that produced the data
-            eng.comm_wait_queue(node.write_queue);
+            // device -> host: after the launch that produced the data
+            eng.comm_wait_queue_seq(node.write_queue, node.write_seq);
             Tile<scalar_t>* s = node.dev;
             Tile<scalar_t>* d = node.host;
             slate_te_call(te_memcpy2d_async(d->data(), sizeof(scalar_t) * d->stride(), s->data(),
@@ -449,7 +454,9 @@ void BaseMatrix<scalar_t>::tileGet(int64_t i, int64_t j, int device, bool modify
     if (node.dev && node.dev_state != MOSI::Invalid) {
         // read-after-write / write-after-write across compute queues
         if (queue >= 0 && node.write_queue >= 0 && node.write_queue != queue)
-            eng.queue_wait_queue(queue, node.write_queue);
+            eng.queue_wait_queue_seq(queue, node.write_queue, node.write_seq);
+        // filled by a broadcast or a host-to-device copy: the consumer waits for that mark
+        if (node.comm_seq > needed_comm_seq_) needed_comm_seq_ = node.comm_seq;
     }
     else {
         slate_assert(node.host && node.host_state != MOSI::Invalid);
@@ -462,12 +469,17 @@ void BaseMatrix<scalar_t>::tileGet(int64_t i, int64_t j, int device, bool modify
         device_copies_pending_ = true;
         node.dev_state = MOSI::Shared;
         node.write_queue = -1;
+        node.comm_seq = eng.next_comm_seq();
+        if (node.comm_seq > needed_comm_seq_) needed_comm_seq_ = node.comm_seq;
         if (node.host_state == MOSI::Modified) node.host_state = MOSI::Shared;
     }
     if (modify) {
         node.dev_state = MOSI::Modified;
         if (node.host) node.host_state = MOSI::Invalid;
-        if (queue >= 0) node.write_queue = queue;
+        if (queue >= 0) {
+            node.write_queue = queue;
+            node.write_seq = eng.next_queue_seq(queue);
+        }
     }
 }
 
@@ -529,8 +541,9 @@ void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
             if (!has_dest) continue;
             tileGet(i, j, 0, false, -1);
             auto& node = storage_->at(globalIndex(i, j));
-            if (device_copies_pending_) { eng.mark_comm(); device_copies_pending_ = false; }
-            eng.comm_wait_queue(node.write_queue);
+            // (a host-to-device staging copy just enqueued is on the same comm stream, ahead
+            //  of the sends: stream order is enough)
+            eng.comm_wait_queue_seq(node.write_queue, node.write_seq);
             Tile<scalar_t>* t = node.dev;
             if (!any) { slate_te_call(te_comm_group_start()); any = true; }
             // device instances made by this library are contiguous (stride == mb)
@@ -548,14 +561,20 @@ void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
             nd.receive_count += 1;
             nd.dev_state = MOSI::Shared;
             nd.write_queue = -1;
+            nd.comm_seq = eng.next_comm_seq();
             Tile<scalar_t>* t = nd.dev;
             if (!any) { slate_te_call(te_comm_group_start()); any = true; }
             slate_te_call(te_comm_recv(comm->nccl, t->data(), t->bytes(), root, stream));
         }
     }
     if (any) {
+        eng.trace_begin(-1, "bcast", (int64_t)bcast_list.size());
         slate_te_call(te_comm_group_end());
+        eng.trace_end(-1);
+    }
+    if (any || device_copies_pending_) {
         eng.mark_comm();
+        device_copies_pending_ = false;
     }
 }
 

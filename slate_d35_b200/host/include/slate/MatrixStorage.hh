@@ -44,6 +44,8 @@ struct TileNode {
     short dev_state = MOSI::Invalid;
     int64_t receive_count = 0;     // MatrixStorage.hh:406-420 (tilePrepareToReceive)
     int write_queue = -1;          // compute queue that last wrote the device instance
+    uint64_t write_seq = 0;        //   and the mark of that queue which follows the write
+    uint64_t comm_seq = 0;         // comm-stream mark after which the device instance is filled
     bool host_owned_buffer = false;
 };
 

@@ -95,9 +95,21 @@ public:
     // ---- event-ordered hand-offs ----
     /// call after enqueueing work on queue q / on the comm stream
     void mark_queue(int q);
-    void mark_comm();
+    /// sequence number the NEXT mark_queue(q) will carry: a tile written by the launch being
+    /// prepared remembers (q, that number) and later consumers wait for exactly that mark
+    uint64_t next_queue_seq(int q) const { return queue_seq_[q] + 1; }
+    void queue_wait_queue_seq(int q, int other, uint64_t seq);
+    void comm_wait_queue_seq(int other, uint64_t seq);
+    /// Records a point on the comm stream and returns its sequence number; tiles filled by
+    /// the comm work enqueued before it carry that number (TileNode::comm_seq).
+    uint64_t mark_comm();
+    /// sequence number the NEXT mark_comm() will return
+    uint64_t next_comm_seq() const { return comm_seq_ + 1; }
     /// make queue q wait for everything enqueued so far on the comm stream / other queue
     void queue_wait_comm(int q);
+    /// make queue q wait for the comm work up to sequence number `seq` only (so that a
+    /// broadcast issued ahead for a later step does not hold this launch back)
+    void queue_wait_comm_seq(int q, uint64_t seq);
     void queue_wait_queue(int q, int other);
     /// make the comm stream wait for everything enqueued so far on queue q
     void comm_wait_queue(int q);
@@ -132,12 +144,20 @@ public:
     void defer(unsigned queue_mask, bool comm, std::function<void()> fn);
     void poll_deferred(bool wait_oldest = false);
     void drain_deferred();
+    bool has_deferred() const { return !deferred_.empty(); }
 
     // ---- timing across all streams ----
     void* timer_begin();             // joins all streams, returns start event
     float timer_end(void* start);    // joins all streams, returns elapsed ms (synchronises)
 
     void finalize();
+
+    // ---- optional per-launch device timing (SLATE_B200_TIMING) ----
+    bool tracing() const { return tracing_; }
+    /// q >= 0: compute queue q; q == -1: the comm stream
+    void trace_begin(int q, const char* what, int64_t count);
+    void trace_end(int q);
+    void trace_dump(const char* title);
 
 private:
     Engine() {}
@@ -150,6 +170,13 @@ private:
     void* comm_stream_ = nullptr;
     void* comm_event_ = nullptr;
     uint64_t comm_seq_ = 0;
+    static const int QueueRing = 64;
+    void* queue_ring_event_[MaxQueues][QueueRing] = {};
+    uint64_t queue_ring_seq_[MaxQueues][QueueRing] = {};
+    void* queue_mark_event(int other, uint64_t seq);
+    static const int CommRing = 64;
+    void* comm_ring_event_[CommRing] = {};
+    uint64_t comm_ring_seq_[CommRing] = {};
     void* queue_[MaxQueues] = {};
     void* queue_event_[MaxQueues] = {};
     uint64_t queue_seq_[MaxQueues] = {};
@@ -163,6 +190,10 @@ private:
     std::deque<Deferred> deferred_;
     std::vector<void*> event_pool_;
     std::recursive_mutex mu_;
+    bool tracing_ = false;
+    struct TraceRec { void* e0; void* e1; const char* what; int64_t count; int q; double host_s; };
+    std::vector<TraceRec> trace_;
+    void* trace_epoch_ = nullptr;
 };
 
 /// Process set-up for the harness: device binding and (size > 1) the NCCL communicator.

@@ -11,9 +11,26 @@
 // broadcasts / panel factorisations run ahead of the trailing update.
 #include "slate/slate.hh"
 
+#include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 
 namespace slate {
+
+namespace {
+/// SLATE_B200_TIMING=1: print where the enqueueing host thread spends its time.
+struct HostTimer {
+    bool on = std::getenv("SLATE_B200_TIMING") != nullptr;
+    double acc[8] = {};
+    std::chrono::steady_clock::time_point t0;
+    void start() { if (on) t0 = std::chrono::steady_clock::now(); }
+    void stop(int slot)
+    {
+        if (on) acc[slot] += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    }
+};
+}  // namespace
 
 //------------------------------------------------------------------------------
 template <typename scalar_t>
@@ -63,17 +80,25 @@ void gemm(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t bet
         B.template listBcastMT<Target::Devices>(list_B, layout);
     };
 
+    HostTimer ht;
+    ht.start();
     for (int64_t k = 0; k <= lookahead && k < kt; ++k)
         bcast(k);
+    ht.stop(0);
 
     for (int64_t k = 0; k < kt; ++k) {
+        ht.start();
         if (k > 0 && k + lookahead < kt)
             bcast(k + lookahead);
+        ht.stop(0);
+        ht.start();
 
         // src/gemmC.cc:113-171: beta only on the first block outer product
         internal::gemm<Target::Devices>(
             alpha, A.sub(0, A.mt() - 1, k, k), B.sub(k, k, 0, B.nt() - 1),
             k == 0 ? beta : one, std::move(C), layout, 0, queue_0);
+        ht.stop(1);
+        ht.start();
 
         // src/gemmC.cc:173-185: drop the panel (returns to the pool when the update is done)
         auto A_panel = A.sub(0, A.mt() - 1, k, k);
@@ -83,12 +108,20 @@ void gemm(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t bet
         B_panel.releaseRemoteWorkspace();
         B_panel.releaseLocalWorkspace();
         Engine::instance().poll_deferred();
+        ht.stop(2);
     }
 
     // src/gemmC.cc:187-190
+    ht.start();
     C.tileUpdateAllOrigin();
     C.releaseWorkspace();
     Engine::instance().sync_all();
+    ht.stop(3);
+    Engine::instance().trace_dump("slate::gemm");
+    if (ht.on)
+        std::fprintf(stderr, "[slate_b200 rank %d] gemm host seconds: bcast %.3f  internal::gemm %.3f  "
+                     "release %.3f  final sync %.3f  (kt = %lld)\n", C.mpiRank(), ht.acc[0], ht.acc[1],
+                     ht.acc[2], ht.acc[3], (long long)kt);
 }
 
 //------------------------------------------------------------------------------

@@ -1,6 +1,8 @@
 // engine.cc -- see slate/engine.hh.
 #include "slate/engine.hh"
 
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -48,6 +50,15 @@ void* Memory::alloc(int device, size_t size)
         return new char[size];
     slate_assert(size <= block_size_);
     slate_assert(pool_ != nullptr);
+    // Blocks released by earlier steps may still be waiting for their kernels to finish
+    // (Engine::defer).  Collect those first; growing the pool means a cudaMalloc in the
+    // middle of the run.
+    if (available(device) == 0) {
+        Engine& eng = Engine::instance();
+        eng.poll_deferred(false);
+        while (available(device) == 0 && eng.has_deferred())
+            eng.poll_deferred(true);
+    }
     void* block = nullptr;
     slate_te_call(te_pool_alloc(pool_, &block));
     return block;
@@ -100,6 +111,7 @@ void Engine::initialize(int device)
     }
     device_ = device;
     initialized_ = true;
+    tracing_ = std::getenv("SLATE_B200_TIMING") != nullptr;
     if (te_device_count() == 0)
         return;     // host-only process: matrices can exist, device paths throw
     slate_te_call(te_stream_create(device_, 1, &comm_stream_));
@@ -130,15 +142,79 @@ void* Engine::compute_stream(int q)
 
 void Engine::mark_queue(int q)
 {
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     void* s = compute_stream(q);
-    slate_te_call(te_event_record(queue_event_[q], s));
     ++queue_seq_[q];
+    slate_te_call(te_event_record(queue_event_[q], s));
+    int slot = (int)(queue_seq_[q] % QueueRing);
+    if (!queue_ring_event_[q][slot])
+        slate_te_call(te_event_create(device_, 0, &queue_ring_event_[q][slot]));
+    slate_te_call(te_event_record(queue_ring_event_[q][slot], s));
+    queue_ring_seq_[q][slot] = queue_seq_[q];
 }
 
-void Engine::mark_comm()
+/// Event that covers mark `seq` of queue `other`: that mark itself if it is still in the
+/// ring, else the oldest mark kept (which is later, so it covers it too).
+void* Engine::queue_mark_event(int other, uint64_t seq)
 {
-    slate_te_call(te_event_record(comm_event_, comm_stream()));
+    if (seq > queue_seq_[other])
+        mark_queue(other);                 // written but not marked yet: cover it now
+    if (seq > queue_seq_[other]) seq = queue_seq_[other];
+    int slot = (int)(seq % QueueRing);
+    if (queue_ring_seq_[other][slot] == seq) return queue_ring_event_[other][slot];
+    uint64_t oldest = queue_seq_[other] >= (uint64_t)QueueRing ? queue_seq_[other] - QueueRing + 1 : 1;
+    slot = (int)(oldest % QueueRing);
+    if (queue_ring_seq_[other][slot] == oldest) return queue_ring_event_[other][slot];
+    return queue_event_[other];
+}
+
+void Engine::queue_wait_queue_seq(int q, int other, uint64_t seq)
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    if (q == other || other < 0 || !queue_[other] || seq == 0) return;
+    slate_te_call(te_stream_wait_event(compute_stream(q), queue_mark_event(other, seq)));
+}
+
+void Engine::comm_wait_queue_seq(int other, uint64_t seq)
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    if (other < 0 || !queue_[other] || seq == 0) return;
+    slate_te_call(te_stream_wait_event(comm_stream(), queue_mark_event(other, seq)));
+}
+
+uint64_t Engine::mark_comm()
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
     ++comm_seq_;
+    slate_te_call(te_event_record(comm_event_, comm_stream()));
+    // a separate event per mark, kept for the last CommRing marks
+    int slot = (int)(comm_seq_ % CommRing);
+    if (!comm_ring_event_[slot])
+        slate_te_call(te_event_create(device_, 0, &comm_ring_event_[slot]));
+    slate_te_call(te_event_record(comm_ring_event_[slot], comm_stream()));
+    comm_ring_seq_[slot] = comm_seq_;
+    return comm_seq_;
+}
+
+void Engine::queue_wait_comm_seq(int q, uint64_t seq)
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    if (seq == 0 || queue_saw_comm_[q] >= seq) return;
+    void* s = compute_stream(q);
+    if (seq > comm_seq_) {
+        // not marked yet: mark now so that the wait covers it
+        mark_comm();
+    }
+    int slot = (int)(seq % CommRing);
+    if (comm_ring_seq_[slot] == seq) {
+        slate_te_call(te_stream_wait_event(s, comm_ring_event_[slot]));
+        queue_saw_comm_[q] = seq;
+    }
+    else {
+        // too old to be in the ring (or overwritten): wait for everything so far
+        slate_te_call(te_stream_wait_event(s, comm_event_));
+        queue_saw_comm_[q] = comm_seq_;
+    }
 }
 
 void Engine::queue_wait_comm(int q)
@@ -339,6 +415,62 @@ float Engine::timer_end(void* start)
     te_event_destroy(stop);
     drain_deferred();
     return ms;
+}
+
+void Engine::trace_begin(int q, const char* what, int64_t count)
+{
+    if (!tracing_) return;
+    TraceRec r;
+    r.what = what;  r.count = count;  r.q = q;
+    r.e0 = new_event(true);
+    r.e1 = new_event(true);
+    r.host_s = std::chrono::duration<double>(
+                   std::chrono::steady_clock::now().time_since_epoch()).count();
+    void* stream = (q < 0) ? comm_stream() : compute_stream(q);
+    if (!trace_epoch_) {
+        trace_epoch_ = new_event(true);
+        slate_te_call(te_event_record(trace_epoch_, stream));
+    }
+    slate_te_call(te_event_record(r.e0, stream));
+    trace_.push_back(r);
+}
+
+void Engine::trace_end(int q)
+{
+    if (!tracing_ || trace_.empty()) return;
+    void* stream = (q < 0) ? comm_stream() : compute_stream(q);
+    // the matching begin is the last record of that queue
+    for (size_t i = trace_.size(); i-- > 0;) {
+        if (trace_[i].q == q) {
+            slate_te_call(te_event_record(trace_[i].e1, stream));
+            break;
+        }
+    }
+}
+
+void Engine::trace_dump(const char* title)
+{
+    if (!tracing_ || trace_.empty()) return;
+    sync_all();
+    std::fprintf(stderr, "[slate_b200 rank %d] %s: %zu launches (start ms, duration ms, host enqueue ms)\n",
+                 comm_world()->rank, title, trace_.size());
+    double h0 = trace_.front().host_s;
+    size_t shown = 0;
+    for (size_t i = 0; i < trace_.size(); ++i) {
+        float t0 = 0, dt = 0;
+        te_event_elapsed_ms(trace_epoch_, trace_[i].e0, &t0);
+        te_event_elapsed_ms(trace_[i].e0, trace_[i].e1, &dt);
+        if (i < 40 || i + 4 >= trace_.size()) {
+            std::fprintf(stderr, "   q%d %-10s n=%-6lld start %9.3f  dur %8.3f  host %9.3f\n", trace_[i].q,
+                         trace_[i].what, (long long)trace_[i].count, t0, dt, (trace_[i].host_s - h0) * 1e3);
+            ++shown;
+        }
+        te_event_destroy(trace_[i].e0);
+        te_event_destroy(trace_[i].e1);
+    }
+    te_event_destroy(trace_epoch_);
+    trace_epoch_ = nullptr;
+    trace_.clear();
 }
 
 void Engine::finalize()

@@ -41,6 +41,7 @@ void launch_batch(DescBatch& batch, int q, Op opa, Op opb, scalar_t alpha, scala
     Engine& eng = Engine::instance();
     const int dtype = te_dtype_of<scalar_t>::value;
     void* stream = eng.compute_stream(q);
+    eng.trace_begin(q, "gemm_tiles", (int64_t)batch.descs.size());
     if ((int)batch.descs.size() <= TE_MAX_INLINE_DESC) {
         // few tiles (panel / lookahead calls): descriptors ride in the kernel parameters
         slate_te_call(te_gemm_inline(eng.device(), stream, dtype, int(opa), int(opb), &alpha, &beta,
@@ -56,6 +57,7 @@ void launch_batch(DescBatch& batch, int q, Op opa, Op opb, scalar_t alpha, scala
                                       batch.max_m, batch.max_n));
         eng.retire_desc(q, slot);
     }
+    eng.trace_end(q);
     eng.mark_queue(q);
 }
 
