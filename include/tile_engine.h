@@ -257,6 +257,8 @@ typedef struct te_comm te_comm;
 int te_comm_unique_id(void* id_out, size_t bytes);
 int te_comm_init_rank(const void* id, size_t bytes, int nranks, int rank, int device,
                       te_comm** comm);
+/* establishes every pairwise connection now (NCCL does it lazily otherwise); synchronous */
+int te_comm_connect_all(te_comm* comm, void* stream);
 int te_comm_destroy(te_comm* comm);
 int te_comm_rank(const te_comm* comm);
 int te_comm_size(const te_comm* comm);

@@ -60,6 +60,31 @@ extern "C" int te_comm_init_rank(const void* id, size_t bytes, int nranks, int r
     return TE_OK;
 }
 
+// NCCL sets up each peer-to-peer connection lazily, at the first send/recv between the
+// pair (about a second for a new pair on this box).  Exchange one small message between
+// every pair now so that no broadcast inside a factorisation pays for it.
+extern "C" int te_comm_connect_all(te_comm* c, void* stream)
+{
+    if (!c) return TE_ERR_ARG;
+    if (c->size == 1) return TE_OK;
+    int st = te::set_device(c->device);
+    if (st != TE_OK) return st;
+    char* buf = nullptr;
+    TE_CUDA_CHECK(cudaMalloc(&buf, 2 * 256 * (size_t)c->size));
+    TE_CUDA_CHECK(cudaMemsetAsync(buf, 0, 2 * 256 * (size_t)c->size, (cudaStream_t)stream));
+    TE_NCCL_CHECK(ncclGroupStart());
+    for (int r = 0; r < c->size; ++r) {
+        if (r == c->rank) continue;
+        TE_NCCL_CHECK(ncclSend(buf + 256 * r, 256, ncclChar, r, c->nccl, (cudaStream_t)stream));
+        TE_NCCL_CHECK(ncclRecv(buf + 256 * (c->size + r), 256, ncclChar, r, c->nccl,
+                               (cudaStream_t)stream));
+    }
+    TE_NCCL_CHECK(ncclGroupEnd());
+    TE_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+    TE_CUDA_CHECK(cudaFree(buf));
+    return TE_OK;
+}
+
 extern "C" int te_comm_destroy(te_comm* c)
 {
     if (!c) return TE_OK;

@@ -74,26 +74,80 @@ potf2_trtri_kernel(T* A, int lda, int upper, T* inv, int* info, int info_base,
     __syncthreads();
 
     if (do_potf2) {
-        for (int j = 0; j < n; ++j) {
-            const double d = real_(S[j * LD + j]);
-            if (!(d > 0.0)) {                              // also catches NaN
-                if (tid == 0) { s_fail = j + 1; }
-                break;                                     // uniform: every thread reads the same d
+        // Right-looking Cholesky with the matrix held in REGISTERS: the 512 threads form a
+        // 32 x 16 grid, thread (tr, tc) owns the elements (tr + 32 m, tc + 16 q).  Per column:
+        // the owners publish the column through a double-buffered shared vector, one
+        // block-wide barrier, and every thread applies the rank-1 update to its own patch.
+        constexpr int RP = IB / 32;                 // rows per thread
+        constexpr int CP = IB / 16;                 // columns per thread
+        T* colbuf = xd + IB;                        // [2][IB]
+        const int tr = tid & 31, tc = tid >> 5;
+        T a[RP][CP];
+#pragma unroll
+        for (int m = 0; m < RP; ++m)
+#pragma unroll
+            for (int q = 0; q < CP; ++q) {
+                const int i = tr + 32 * m, c = tc + 16 * q;
+                a[m][q] = (i < n && c <= i) ? S[i * LD + c] : zero_<T>();
             }
-            const double r = sqrt(d);
-            const double rinv = 1.0 / r;
-            __syncthreads();                               // everyone has read S[j][j]
-            for (int i = j + 1 + tid; i < n; i += PANEL_THREADS)
-                S[i * LD + j] = S[i * LD + j] * rinv;
-            if (tid == 0) set_real(S[j * LD + j], r);
-            __syncthreads();
-            const int rem = n - j - 1;
-            for (int idx = tid; idx < rem * rem; idx += PANEL_THREADS) {
-                const int i = idx % rem, c = idx / rem;
-                if (i >= c) {
-                    const int gi = j + 1 + i, gc = j + 1 + c;
-                    S[gi * LD + gc] = S[gi * LD + gc] - S[gi * LD + j] * conj_(S[gc * LD + j]);
+        // publish column 0
+        if (tc == 0) {
+#pragma unroll
+            for (int m = 0; m < RP; ++m) colbuf[tr + 32 * m] = a[m][0];
+        }
+        __syncthreads();
+        for (int j = 0; j < n; ++j) {
+            const T* col = colbuf + (j & 1) * IB;
+            const double d = real_(col[j]);
+            if (!(d > 0.0)) {                              // also catches NaN; uniform
+                if (tid == 0) s_fail = j + 1;
+                break;
+            }
+            // rsqrt is a few instructions (sqrt + divide are ~40, executed by every warp in
+            // every step); d * rsqrt(d) is within 2 ulp of sqrt(d)
+            const double rinv = rsqrt(d);
+            const double rdiag = d * rinv;
+            const int qj = j >> 4;
+            const bool own = (tc == (j & 15));
+            T li[RP], lc[CP];
+#pragma unroll
+            for (int m = 0; m < RP; ++m) li[m] = col[tr + 32 * m] * rinv;
+#pragma unroll
+            for (int q = 0; q < CP; ++q) lc[q] = conj_(col[tc + 16 * q] * rinv);
+            // branch-free rank-1 update of the columns right of j (select, not branch: the
+            // unrolled 4 x 8 patch must stay a handful of instructions per element)
+#pragma unroll
+            for (int q = 0; q < CP; ++q) {
+                // tc is the warp index, so this test is warp-uniform: a real branch that
+                // skips the column groups already factored
+                if (tc + 16 * q > j) {
+#pragma unroll
+                    for (int m = 0; m < RP; ++m) a[m][q] = a[m][q] - li[m] * lc[q];
                 }
+            }
+            if (own) {
+                // this thread holds part of column j itself: keep the scaled column
+#pragma unroll
+                for (int q = 0; q < CP; ++q)
+                    if (q == qj) {
+#pragma unroll
+                        for (int m = 0; m < RP; ++m) {
+                            const int i = tr + 32 * m;
+                            if (i == j) set_real(a[m][q], rdiag);
+                            else if (i > j) a[m][q] = li[m];
+                        }
+                    }
+            }
+            // publish column j + 1 (now final) into the other buffer
+            if (j + 1 < n && tc == ((j + 1) & 15)) {
+                T* nxt = colbuf + ((j + 1) & 1) * IB;
+                const int qn = (j + 1) >> 4;
+#pragma unroll
+                for (int q = 0; q < CP; ++q)
+                    if (q == qn) {
+#pragma unroll
+                        for (int m = 0; m < RP; ++m) nxt[tr + 32 * m] = a[m][q];
+                    }
             }
             __syncthreads();
         }
@@ -102,10 +156,22 @@ potf2_trtri_kernel(T* A, int lda, int upper, T* inv, int* info, int info_base,
             if (tid == 0) *info = info_base + s_fail;
             return;                                        // LAPACK leaves the tile partly factored
         }
+#pragma unroll
+        for (int m = 0; m < RP; ++m)
+#pragma unroll
+            for (int q = 0; q < CP; ++q) {
+                const int i = tr + 32 * m, c = tc + 16 * q;
+                if (i < n && c <= i) S[i * LD + c] = a[m][q];
+            }
+        __syncthreads();
     }
 
     // ---- inverse of the lower factor: X = S^-1, X^T kept in the strict upper part ----
-    // row i of X:  X[i][j] = -(sum_{l=j}^{i-1} S[i][l] X[l][j]) / S[i][i],  X[i][i] = 1/S[i][i]
+    // Column j of X belongs to 4 adjacent lanes; lane `part` keeps the running sums
+    //   s_i = sum_{l < current} S[i][l] X[l][j]   for the rows i = part + 4 m
+    // in registers.  Step l: x_l = -s_l / S[l][l] comes from the lane that owns row l
+    // (shuffle), then every lane adds S[i][l] x_l to its rows below l: 32 independent
+    // LDS + FMA per step and no barrier at all.
     for (int i = tid; i < n; i += PANEL_THREADS) {
         if (unit_diag) xd[i] = from_real<T>(1.0);
         else {
@@ -116,22 +182,55 @@ potf2_trtri_kernel(T* A, int lda, int upper, T* inv, int* info, int info_base,
         }
     }
     __syncthreads();
-    for (int i = 1; i < n; ++i) {
-        // 4 lanes per column j split the sum over l
+    {
+        constexpr int MP = IB / 4;                  // rows per lane
         const int j = tid >> 2, part = tid & 3;
-        T sum = zero_<T>();
-        if (j < i) {
-            for (int l = j + part; l < i; l += 4) {
-                const T x = (l == j) ? xd[j] : S[j * LD + l];      // X[l][j]
-                sum = sum + S[i * LD + l] * x;
+        if (j < IB) {                               // warps past the last column are idle
+            T sums[MP];
+#pragma unroll
+            for (int m = 0; m < MP; ++m) sums[m] = zero_<T>();
+            const bool active = (j < n);
+            // the 4 lanes of a column move together; columns in one warp differ by < 8, so
+            // all start at the first column of the warp (earlier steps are no-ops for them)
+            const int l_begin = ((tid & ~31) >> 2) & ~3;      // multiple of 4
+            const int gbase = threadIdx.x & 31 & ~3;
+            for (int l4 = l_begin; l4 < n; l4 += 4) {
+                // the running sums of rows l4 .. l4+3 sit in sums[l4 / 4] of lanes 0 .. 3
+                T own_sum = zero_<T>();
+                const int m0 = l4 >> 2;
+#pragma unroll
+                for (int m = 0; m < MP; ++m)
+                    if (m == m0) own_sum = sums[m];
+#pragma unroll
+                for (int pp = 0; pp < 4; ++pp) {
+                    const int l = l4 + pp;
+                    // rows l4 .. l4+pp-1 were finished in this group of four: fold their
+                    // contribution to row l in before it is read (done below via own_sum)
+                    T xl;
+                    if constexpr (sizeof(T) == 8) {
+                        xl = __shfl_sync(0xffffffffu, own_sum, gbase | pp);
+                    }
+                    else {
+                        xl.x = __shfl_sync(0xffffffffu, own_sum.x, gbase | pp);
+                        xl.y = __shfl_sync(0xffffffffu, own_sum.y, gbase | pp);
+                    }
+                    if (l >= n || l < j) continue;             // no shuffles below this point
+                    xl = (l == j) ? xd[l] : -(xl * xd[l]);
+                    if (active && part == 0 && l > j) S[j * LD + l] = xl;   // X[l][j], transposed
+                    // the lanes that own rows l+1 .. l4+3 need this x_l before their turn
+                    if (part > pp) own_sum = own_sum + S[l * LD + (part - pp) * LD + l] * xl;
+                    // rows below l: m >= mth.  Rows >= n only hold padding and sums[m0] is not
+                    // read again, so neither needs a test of its own.
+                    const T* Lcol = S + part * LD + l;          // row part, column l
+                    const int mth = (l - part + 4) >> 2;
+#pragma unroll
+                    for (int m = 0; m < MP; ++m)
+                        if (m >= mth) sums[m] = sums[m] + Lcol[m * 4 * LD] * xl;
+                }
             }
         }
-        sum = sum + shfl_xor_(sum, 1);
-        sum = sum + shfl_xor_(sum, 2);
-        if (j < i && part == 0)
-            S[j * LD + i] = -(sum * xd[i]);
-        __syncthreads();
     }
+    __syncthreads();
 
     // ---- write back ----
     for (int idx = tid; idx < n * n; idx += PANEL_THREADS) {
@@ -159,7 +258,7 @@ template <typename T>
 static int panel_smem_bytes()
 {
     constexpr int IB = PanelCfg<T>::IB;
-    return (IB * (IB + 1) + IB) * (int)sizeof(T);
+    return (IB * (IB + 1) + 3 * IB) * (int)sizeof(T);
 }
 
 template <typename T>

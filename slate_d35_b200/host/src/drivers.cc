@@ -219,6 +219,7 @@ int64_t potrf(HermitianMatrix<scalar_t>& A_in, Options const& opts)
     if (!hold_local_workspace)
         A.releaseWorkspace();
     eng.sync_all();
+    eng.trace_dump("slate::potrf");
 
     // first failing step -> LAPACK info (src/potrf.cc:104-105, 208)
     std::vector<int> step_info(A_nt, 0);

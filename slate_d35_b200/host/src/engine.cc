@@ -489,6 +489,7 @@ void initialize(int device, int rank, int size, const void* nccl_id)
         slate_assert(nccl_id != nullptr);
         slate_te_call(te_comm_init_rank(nccl_id, TE_COMM_ID_BYTES, size, rank,
                                         Engine::instance().device(), &g_world.nccl));
+        slate_te_call(te_comm_connect_all(g_world.nccl, Engine::instance().comm_stream()));
     }
 }
 

@@ -300,10 +300,12 @@ void trsm(TargetType<Target::Devices>, Side side, scalar_t alpha, TriangularMatr
     eng.upload_desc(q, slot, bytes);
     size_t sb = te_trsm_scratch_bytes(dtype, na, (int64_t)descs.size());
     void* scratch = eng.scratch(q, sb);
+    eng.trace_begin(q, "trsm", (int64_t)descs.size());
     slate_te_call(te_trsm_batched(eng.device(), eng.compute_stream(q), dtype, int(sideA), int(uploA),
                                   int(opA), int(diagA), &alpha, A00.data(), (int)A00.stride(), na,
                                   (const te_trsm_desc*)slot.dev, (int64_t)descs.size(), max_m, max_n,
                                   scratch, sb));
+    eng.trace_end(q);
     eng.retire_desc(q, slot);
     eng.mark_queue(q);
 }
@@ -326,9 +328,11 @@ int64_t potrf(TargetType<Target::Devices>, HermitianMatrix<scalar_t>& A, int pri
     size_t sb = te_potrf_scratch_bytes(dtype);
     // the trsm that follows on the same queue uses the same scratch: stream order keeps them apart
     void* scratch = eng.scratch(q, sb);
+    eng.trace_begin(q, "potrf_tile", 1);
     slate_te_call(te_potrf_tile(eng.device(), eng.compute_stream(q), dtype,
                                 int(A00.uploPhysical()), (int)A.tileMb(0), A00.data(),
                                 (int)A00.stride(), info_dev, scratch, sb));
+    eng.trace_end(q);
     eng.mark_queue(q);
     if (device_info) return 0;
     int info = 0;
