@@ -43,6 +43,10 @@ def hostlib():
                           C.POINTER(C.c_float)]
     L.sb_potrf.argtypes = [vp, C.c_int, C.c_int, C.POINTER(i64), C.POINTER(C.c_float)]
     L.sb_potrf_residual.argtypes = [vp, i64, C.c_int, dp, dp]
+    ip = C.POINTER(i64)
+    L.sb_plan_gemm_step.argtypes = [vp, vp, vp, i64, ip, i64, ip]
+    L.sb_plan_potrf_step.argtypes = [vp, i64, ip, i64, ip]
+    L.sb_tile_rank.argtypes = [vp, i64, i64]
     L.sb_internal_gemm.argtypes = [C.c_int, C.c_int, C.c_int, dp, vp, vp, dp, vp, C.c_int, C.c_int]
     L.sb_internal_herk.argtypes = [C.c_int, C.c_int, C.c_double, vp, C.c_double, vp, C.c_int]
     L.sb_internal_syrk.argtypes = [C.c_int, C.c_int, dp, vp, dp, vp, C.c_int]
@@ -76,9 +80,10 @@ def initialize(device=None, rank=0, size=1, nccl_id=None):
     if device is None:
         device = int(os.environ.get("LOCAL_RANK", "0"))
     buf = None
-    if size > 1:
+    if size > 1 and _te_lib().te_device_count() > 0:
         assert nccl_id is not None and len(nccl_id) == 128
         buf = C.create_string_buffer(bytes(nccl_id), 128)
+    # (without a GPU a multi-rank process can still build index maps and broadcast plans)
     _check(hostlib().sb_initialize(device, rank, size, buf))
     _initialized = True
 
@@ -234,6 +239,39 @@ def potrf_residual(A, seed, dominant=True):
     r, a0 = C.c_double(), C.c_double()
     _check(hostlib().sb_potrf_residual(A.h, seed, int(dominant), C.byref(r), C.byref(a0)))
     return r.value, a0.value
+
+
+def _unflatten(buf, used):
+    ops, pos = [], 0
+    while pos < used:
+        which, i, j, root, nd = (int(x) for x in buf[pos:pos + 5])
+        ops.append((which, i, j, root, [int(x) for x in buf[pos + 5:pos + 5 + nd]]))
+        pos += 5 + nd
+    return ops
+
+
+def plan_gemm_step(A, B, Cm, k):
+    """Broadcasts slate::gemm issues for SUMMA step k: [(which, i, j, root, [dest ranks])],
+    which = 0 for A(i, k), 1 for B(k, j).  Host logic only (no GPU needed)."""
+    cap = 8 * (A.m // A.nb + Cm.n // Cm.nb + 8) * (Cm.p * Cm.q + 6)
+    buf = (i64 * cap)()
+    used = i64()
+    _check(hostlib().sb_plan_gemm_step(A.h, B.h, Cm.h, k, buf, cap, C.byref(used)))
+    return _unflatten(buf, used.value)
+
+
+def plan_potrf_step(A, k):
+    """Broadcasts slate::potrf issues in step k: which = 0 the diagonal tile (before the
+    panel solve), which = 1 the panel tiles (after it)."""
+    cap = 8 * (A.n // A.nb + 8) * (A.p * A.q + 6)
+    buf = (i64 * cap)()
+    used = i64()
+    _check(hostlib().sb_plan_potrf_step(A.h, k, buf, cap, C.byref(used)))
+    return _unflatten(buf, used.value)
+
+
+def tile_rank(A, i, j):
+    return hostlib().sb_tile_rank(A.h, i, j)
 
 
 def internal_gemm(alpha, A, B, beta, Cm, opa="N", opb="N", opc="N", target="D", queue=0):

@@ -370,6 +370,36 @@ public:
     void listBcastMT(BcastListTag& bcast_list, Layout layout = Layout::ColMajor,
                      int64_t life_factor = 1, bool is_shared = false);
 
+    /// One tile broadcast of a plan: tile (i, j) of this view goes from rank `root` to `dests`.
+    struct BcastOp { int64_t i, j; int root; std::vector<int> dests; };
+
+    /// The host-side half of listBcast (BaseMatrix.hh:2129-2213 + getRanks :3702-3756): which
+    /// rank sends which tile to which ranks.  Pure index arithmetic on the 2D block-cyclic map,
+    /// no device and no communicator needed; listBcastMT executes exactly this plan, and the
+    /// CPU tests execute it over gloo.  Entries whose destination set is empty are dropped.
+    std::vector<BcastOp> bcastPlan(BcastListTag const& bcast_list) const
+    {
+        std::vector<BcastOp> plan;
+        const int nranks = storage_->comm_->size;
+        std::vector<char> in_set(nranks);
+        for (auto const& e : bcast_list) {
+            BcastOp op;
+            op.i = std::get<0>(e);
+            op.j = std::get<1>(e);
+            op.root = tileRank(op.i, op.j);
+            std::fill(in_set.begin(), in_set.end(), 0);
+            for (auto const& B : std::get<2>(e))
+                for (int64_t jj = 0; jj < B.nt(); ++jj)
+                    for (int64_t ii = 0; ii < B.mt(); ++ii)
+                        if (B.inStoredTriangle(ii, jj)) in_set[B.tileRank(ii, jj)] = 1;
+            in_set[op.root] = 0;
+            for (int r = 0; r < nranks; ++r)
+                if (in_set[r]) op.dests.push_back(r);
+            if (!op.dests.empty()) plan.push_back(std::move(op));
+        }
+        return plan;
+    }
+
     /// ranks owning at least one tile of this view (BaseMatrix.hh:3702-3756)
     void getRanks(std::set<int>* bcast_set) const
     {
@@ -523,22 +553,9 @@ void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
     slate_assert(comm->nccl != nullptr);
     void* stream = eng.comm_stream();
     bool any = false;
-    std::vector<char> in_set(comm->size);
-    for (auto& e : bcast_list) {
-        int64_t i = std::get<0>(e), j = std::get<1>(e);
-        auto& dests = std::get<2>(e);
-        const int root = tileRank(i, j);
-        std::fill(in_set.begin(), in_set.end(), 0);
-        for (auto const& B : dests) {
-            for (int64_t jj = 0; jj < B.nt(); ++jj)
-                for (int64_t ii = 0; ii < B.mt(); ++ii)
-                    if (B.inStoredTriangle(ii, jj)) in_set[B.tileRank(ii, jj)] = 1;
-        }
-        in_set[root] = 0;
-        if (me == root) {
-            bool has_dest = false;
-            for (int r = 0; r < comm->size; ++r) has_dest |= (in_set[r] != 0);
-            if (!has_dest) continue;
+    for (auto const& op : bcastPlan(bcast_list)) {
+        const int64_t i = op.i, j = op.j;
+        if (me == op.root) {
             tileGet(i, j, 0, false, -1);
             auto& node = storage_->at(globalIndex(i, j));
             // (a host-to-device staging copy just enqueued is on the same comm stream, ahead
@@ -548,11 +565,10 @@ void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
             if (!any) { slate_te_call(te_comm_group_start()); any = true; }
             // device instances made by this library are contiguous (stride == mb)
             slate_assert(t->isContiguous());
-            for (int r = 0; r < comm->size; ++r)
-                if (in_set[r])
-                    slate_te_call(te_comm_send(comm->nccl, t->data(), t->bytes(), r, stream));
+            for (int r : op.dests)
+                slate_te_call(te_comm_send(comm->nccl, t->data(), t->bytes(), r, stream));
         }
-        else if (in_set[me]) {
+        else if (std::find(op.dests.begin(), op.dests.end(), me) != op.dests.end()) {
             // tilePrepareToReceive (MatrixStorage.hh:406-420): workspace tile on the device
             auto* node = storage_->find(globalIndex(i, j));
             if (!node || !node->dev)
@@ -564,7 +580,7 @@ void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
             nd.comm_seq = eng.next_comm_seq();
             Tile<scalar_t>* t = nd.dev;
             if (!any) { slate_te_call(te_comm_group_start()); any = true; }
-            slate_te_call(te_comm_recv(comm->nccl, t->data(), t->bytes(), root, stream));
+            slate_te_call(te_comm_recv(comm->nccl, t->data(), t->bytes(), op.root, stream));
         }
     }
     if (any) {

@@ -34,6 +34,19 @@ int64_t chol_factor(HermitianMatrix<scalar_t>& A, Options const& opts = Options(
     return potrf(A, opts);
 }
 
+// ---- the broadcast lists of one driver step (shared by the drivers and the planners) -----
+/// src/gemmC.cc:143-157: block column k of A to the owners of each row of C (which = 0) or
+/// block row k of B to the owners of each column of C (which = 1).
+template <typename scalar_t>
+typename Matrix<scalar_t>::BcastListTag gemm_bcast_list(int which, Matrix<scalar_t>& A,
+                                                        Matrix<scalar_t>& B, Matrix<scalar_t>& C,
+                                                        int64_t k);
+/// src/potrf.cc:109 (which = 0: A(k,k) down its column) and :122-132 (which = 1: A(i,k) across
+/// row i and down column i); A is the lower view.
+template <typename scalar_t>
+typename Matrix<scalar_t>::BcastListTag potrf_bcast_list(int which, HermitianMatrix<scalar_t>& A,
+                                                         int64_t k);
+
 // ---- harness helpers (not part of the reference surface) --------------------------------
 /// Fills the local tiles with matgen's "rand" family (matgen/generate_type_rand.hh:40-135):
 /// entry (i, j) is a pure function of (seed, i, j); `dominant` adds n to the diagonal.

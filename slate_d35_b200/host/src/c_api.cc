@@ -83,6 +83,7 @@ void create(Handle* h, int kind, int uplo, int diag, int64_t m, int64_t n, int64
     Uplo u = (uplo == 'U') ? Uplo::Upper : Uplo::Lower;
     Diag d = (diag == 'U') ? Diag::Unit : Diag::NonUnit;
     Target org = (origin == 'D') ? Target::Devices : Target::Host;
+    const bool no_tiles = (origin == 'N');        // index map only (planning)
     MPI_Comm comm = MPI_COMM_WORLD;
     if (p * q == 1 && comm->size > 1) comm = MPI_COMM_SELF;
     switch (kind) {
@@ -91,7 +92,7 @@ void create(Handle* h, int kind, int uplo, int diag, int64_t m, int64_t n, int64
                                 origin == 'S' ? Matrix<T>::fromScaLAPACK(m, n, host, ld, nb, p, q, comm)
                                               : Matrix<T>::fromLAPACK(m, n, host, ld, nb, p, q, comm))
                           : std::make_shared<Matrix<T>>(m, n, nb, p, q, comm);
-            if (!host) M->insertLocalTiles(org);
+            if (!host && !no_tiles) M->insertLocalTiles(org);
             h->obj = M;
             break;
         }
@@ -99,7 +100,7 @@ void create(Handle* h, int kind, int uplo, int diag, int64_t m, int64_t n, int64
             auto M = host ? std::make_shared<HermitianMatrix<T>>(
                                 HermitianMatrix<T>::fromLAPACK(u, n, host, ld, nb, p, q, comm))
                           : std::make_shared<HermitianMatrix<T>>(u, n, nb, p, q, comm);
-            if (!host) M->insertLocalTiles(org);
+            if (!host && !no_tiles) M->insertLocalTiles(org);
             h->obj = M;
             break;
         }
@@ -107,7 +108,7 @@ void create(Handle* h, int kind, int uplo, int diag, int64_t m, int64_t n, int64
             auto M = host ? std::make_shared<SymmetricMatrix<T>>(
                                 SymmetricMatrix<T>::fromLAPACK(u, n, host, ld, nb, p, q, comm))
                           : std::make_shared<SymmetricMatrix<T>>(u, n, nb, p, q, comm);
-            if (!host) M->insertLocalTiles(org);
+            if (!host && !no_tiles) M->insertLocalTiles(org);
             h->obj = M;
             break;
         }
@@ -115,7 +116,7 @@ void create(Handle* h, int kind, int uplo, int diag, int64_t m, int64_t n, int64
             auto M = host ? std::make_shared<TriangularMatrix<T>>(
                                 TriangularMatrix<T>::fromLAPACK(u, d, n, host, ld, nb, p, q, comm))
                           : std::make_shared<TriangularMatrix<T>>(u, d, n, nb, p, q, comm);
-            if (!host) M->insertLocalTiles(org);
+            if (!host && !no_tiles) M->insertLocalTiles(org);
             h->obj = M;
             break;
         }
@@ -172,6 +173,23 @@ void copy_all(Handle* h, T* host, int64_t ld, bool to_host)
 }
 
 }  // namespace
+
+namespace {
+template <typename M>
+int64_t flatten_plan(M& mat, typename M::BcastListTag& list, int which, int64_t* out, int64_t cap,
+                     int64_t pos)
+{
+    for (auto const& op : mat.bcastPlan(list)) {
+        int64_t need = 5 + (int64_t)op.dests.size();
+        if (pos + need > cap) slate_error("plan buffer too small");
+        out[pos++] = which;  out[pos++] = op.i;  out[pos++] = op.j;  out[pos++] = op.root;
+        out[pos++] = (int64_t)op.dests.size();
+        for (int d : op.dests) out[pos++] = d;
+    }
+    return pos;
+}
+}  // namespace
+
 
 #define DISPATCH(h, call_d, call_z)          \
     do {                                     \
@@ -313,6 +331,42 @@ int sb_potrf_residual(void* A, int64_t seed, int dominant, double* resid_sumsq, 
                  *resid_sumsq = potrf_residual_sumsq(as_herm<double>(h), seed, dominant != 0, a0_sumsq),
                  *resid_sumsq = potrf_residual_sumsq(as_herm<zdouble>(h), seed, dominant != 0, a0_sumsq));
     });
+}
+
+// ---- broadcast plans (host logic only; runs without a GPU) ---------------------------------
+/// Broadcasts of SUMMA step k as slate::gemm issues them: records
+/// [which (0 = A, 1 = B), i, j, root, ndest, dest...], A's list first.
+int sb_plan_gemm_step(void* A, void* B, void* C, int64_t k, int64_t* out, int64_t cap, int64_t* used)
+{
+    Handle *ha = (Handle*)A, *hb = (Handle*)B, *hc = (Handle*)C;
+    return guarded([&] {
+        auto& a = as_general<double>(ha);  auto& b = as_general<double>(hb);
+        auto& c = as_general<double>(hc);
+        auto la = gemm_bcast_list(0, a, b, c, k);
+        auto lb = gemm_bcast_list(1, a, b, c, k);
+        int64_t pos = flatten_plan(a, la, 0, out, cap, 0);
+        *used = flatten_plan(b, lb, 1, out, cap, pos);
+    });
+}
+
+/// Broadcasts of Cholesky step k as slate::potrf issues them (lower storage): which = 0 is
+/// A(k,k) down its column (before the trsm), which = 1 the panel tiles A(i,k) (after it).
+int sb_plan_potrf_step(void* A, int64_t k, int64_t* out, int64_t cap, int64_t* used)
+{
+    Handle* h = (Handle*)A;
+    return guarded([&] {
+        auto& a = as_herm<double>(h);
+        auto l0 = potrf_bcast_list(0, a, k);
+        auto l1 = potrf_bcast_list(1, a, k);
+        int64_t pos = flatten_plan(a, l0, 0, out, cap, 0);
+        *used = flatten_plan(a, l1, 1, out, cap, pos);
+    });
+}
+
+int sb_tile_rank(void* A, int64_t i, int64_t j)
+{
+    Handle* h = (Handle*)A;
+    return h->dtype == TE_C64 ? as_base<zdouble>(h).tileRank(i, j) : as_base<double>(h).tileRank(i, j);
 }
 
 // ---- internal ops, as unit_test/test_internal_blas.cc drives them ------------------------

@@ -34,6 +34,41 @@ struct HostTimer {
 
 //------------------------------------------------------------------------------
 template <typename scalar_t>
+typename Matrix<scalar_t>::BcastListTag gemm_bcast_list(int which, Matrix<scalar_t>& A,
+                                                        Matrix<scalar_t>& B, Matrix<scalar_t>& C,
+                                                        int64_t k)
+{
+    typename Matrix<scalar_t>::BcastListTag list;
+    if (which == 0) {
+        for (int64_t i = 0; i < A.mt(); ++i)
+            list.push_back({i, k, {C.sub(i, i, 0, C.nt() - 1)}, i});
+    }
+    else {
+        for (int64_t j = 0; j < B.nt(); ++j)
+            list.push_back({k, j, {C.sub(0, C.mt() - 1, j, j)}, j});
+    }
+    return list;
+}
+
+template <typename scalar_t>
+typename Matrix<scalar_t>::BcastListTag potrf_bcast_list(int which, HermitianMatrix<scalar_t>& A,
+                                                         int64_t k)
+{
+    typename Matrix<scalar_t>::BcastListTag list;
+    const int64_t A_nt = A.nt();
+    if (which == 0) {
+        if (k + 1 <= A_nt - 1)
+            list.push_back({k, k, {A.sub(k + 1, A_nt - 1, k, k)}, k});
+    }
+    else {
+        for (int64_t i = k + 1; i < A_nt; ++i)
+            list.push_back({i, k, {A.sub(i, i, k + 1, i), A.sub(i, A_nt - 1, i, i)}, i});
+    }
+    return list;
+}
+
+//------------------------------------------------------------------------------
+template <typename scalar_t>
 void gemm(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t beta,
           Matrix<scalar_t>& C, Options const& opts)
 {
@@ -71,12 +106,9 @@ void gemm(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t bet
     // send block column k of A along the process rows and block row k of B along the
     // process columns that own C (src/gemmC.cc:78-110, 143-157)
     auto bcast = [&](int64_t k) {
-        BcastListTag list_A, list_B;
-        for (int64_t i = 0; i < A.mt(); ++i)
-            list_A.push_back({i, k, {C.sub(i, i, 0, C.nt() - 1)}, i});
+        BcastListTag list_A = gemm_bcast_list(0, A, B, C, k);
         A.template listBcastMT<Target::Devices>(list_A, layout);
-        for (int64_t j = 0; j < B.nt(); ++j)
-            list_B.push_back({k, j, {C.sub(0, C.mt() - 1, j, j)}, j});
+        BcastListTag list_B = gemm_bcast_list(1, A, B, C, k);
         B.template listBcastMT<Target::Devices>(list_B, layout);
     };
 
@@ -166,7 +198,8 @@ int64_t potrf(HermitianMatrix<scalar_t>& A_in, Options const& opts)
 
         if (k + 1 <= A_nt - 1) {
             // send A(k, k) down col A(k+1:nt-1, k)
-            A.template tileBcast<Target::Devices>(k, k, A.sub(k + 1, A_nt - 1, k, k), layout);
+            BcastListTag bcast_diag = potrf_bcast_list(0, A, k);
+            A.template listBcastMT<Target::Devices>(bcast_diag, layout);
 
             // A(k+1:nt-1, k) * A(k, k)^{-H}
             auto Akk = A.sub(k, k);
@@ -175,9 +208,7 @@ int64_t potrf(HermitianMatrix<scalar_t>& A_in, Options const& opts)
                                             A.sub(k + 1, A_nt - 1, k, k), 0, layout, queue_panel);
 
             // send A(i, k) across row A(i, k+1:i) and down col A(i:nt-1, i)
-            BcastListTag bcast_list_A;
-            for (int64_t i = k + 1; i < A_nt; ++i)
-                bcast_list_A.push_back({i, k, {A.sub(i, i, k + 1, i), A.sub(i, A_nt - 1, i, i)}, i});
+            BcastListTag bcast_list_A = potrf_bcast_list(1, A, k);
             A.template listBcastMT<Target::Devices>(bcast_list_A, layout);
         }
 
@@ -414,6 +445,10 @@ double potrf_residual_sumsq(HermitianMatrix<scalar_t>& A, int64_t seed, bool dom
 
 //------------------------------------------------------------------------------
 #define INSTANTIATE(T)                                                                        \
+    template typename Matrix<T>::BcastListTag gemm_bcast_list<T>(int, Matrix<T>&, Matrix<T>&,  \
+                                                                 Matrix<T>&, int64_t);         \
+    template typename Matrix<T>::BcastListTag potrf_bcast_list<T>(int, HermitianMatrix<T>&,    \
+                                                                  int64_t);                    \
     template void gemm<T>(T, Matrix<T>&, Matrix<T>&, T, Matrix<T>&, Options const&);           \
     template int64_t potrf<T>(HermitianMatrix<T>&, Options const&);                            \
     template void generate_rand<T>(BaseMatrix<T>&, int64_t, bool, int);                        \

@@ -485,7 +485,8 @@ void initialize(int device, int rank, int size, const void* nccl_id)
     Engine::instance().initialize(device);
     g_world.rank = rank;
     g_world.size = size;
-    if (size > 1 && g_world.nccl == nullptr) {
+    // a process without a GPU can still build matrices and plans (tests of the host logic)
+    if (size > 1 && g_world.nccl == nullptr && te_device_count() > 0) {
         slate_assert(nccl_id != nullptr);
         slate_te_call(te_comm_init_rank(nccl_id, TE_COMM_ID_BYTES, size, rank,
                                         Engine::instance().device(), &g_world.nccl));
