@@ -74,7 +74,7 @@ struct Item {
     bool a16, b16, c16;            // 16-byte path usable
 };
 
-template <bool INL>
+template <bool INL, int BMv = 128>
 __device__ __forceinline__ bool decode(const GemmParams& p, int64_t w, Item& it)
 {
     const int bpt = p.nbm * p.nbn;
@@ -84,11 +84,11 @@ __device__ __forceinline__ bool decode(const GemmParams& p, int64_t w, Item& it)
     const int sm = sub - sn * p.nbm;
     const te_tile_desc* d = INL ? &p.inl[t] : &p.desc[t];
     const int m = d->m, n = d->n;
-    const int m0 = sm * BM, n0 = sn * BN;
+    const int m0 = sm * BMv, n0 = sn * BN;
     if (m0 >= m || n0 >= n)
         return false;
     const int flags = d->flags;
-    if ((flags & TE_TILE_LOWER) && (m0 + BM - 1 < n0))
+    if ((flags & TE_TILE_LOWER) && (m0 + BMv - 1 < n0))
         return false;
     if ((flags & TE_TILE_UPPER) && (n0 + BN - 1 < m0))
         return false;
@@ -116,7 +116,7 @@ __device__ __forceinline__ bool decode(const GemmParams& p, int64_t w, Item& it)
 // hardware block scheduler then balances the load by itself and lets kernels on
 // higher-priority streams (NCCL broadcasts, the Cholesky panel) take SMs as CTAs retire,
 // which a grid of persistent CTAs with fixed shares would block.
-template <bool INL>
+template <bool INL, int BMv = 128>
 struct Walker {
     int64_t w, w_end;
     int nk;        // K slices of the current item
@@ -127,7 +127,7 @@ struct Walker {
     {
         valid = false;
         while (w < w_end) {
-            if (decode<INL>(p, w, it)) {
+            if (decode<INL, BMv>(p, w, it)) {
                 valid = true;
                 nk = (it.k + KC - 1) / KC;
                 return;
@@ -403,6 +403,236 @@ dgemm_tiles_kernel(const __grid_constant__ GemmParams p)
     }
 }
 
+// =================================================================================
+// complex-FP64:  C_i = alpha op(A_i) op(B_i) + beta C_i,  interleaved (re, im) storage
+// =================================================================================
+// Same structure as the real kernel (producer warpgroup, cp.async ring with mbarriers,
+// runs of consecutive work items per CTA); differences:
+//   * one complex product is four real DMMAs on de-interleaved fragments
+//     (re += ar*br - ai*bi, im += ar*bi + ai*br); a fragment load is one LDS.128 that
+//     brings (re, im) of an element, conjugation flips the sign of im in registers;
+//   * the CTA tile is 64 (m) x 128 (n), warp tile 32 x 32: 16 complex accumulator
+//     fragments = 128 registers, as in the real kernel;
+//   * one cp.async (16 bytes) per element, so any 16-byte aligned complex array takes
+//     the fast path whatever its leading dimension;
+//   * row padding of +2 / +4 complex elements keeps the 128-bit fragment loads
+//     conflict free (8 lanes per phase).
+constexpr int ZBM = 64;
+constexpr int ZSTAGES = 3;
+constexpr int ZLD_A_MN = ZBM + 2;          // [k][m] slice of A, complex elements
+constexpr int ZLD_B_MN = BN + 2;           // [k][n] slice of B
+constexpr int ZLD_K = KC + 4;              // [mn][k] slices
+constexpr int ZSLICE_A = (KC * ZLD_A_MN > ZBM * ZLD_K) ? KC * ZLD_A_MN : ZBM * ZLD_K;   // complex elems
+constexpr int ZSLICE_B = (KC * ZLD_B_MN > BN * ZLD_K) ? KC * ZLD_B_MN : BN * ZLD_K;
+constexpr int ZSMEM_BYTES = ZSTAGES * (ZSLICE_A + ZSLICE_B) * 16 + 2 * ZSTAGES * 8;
+
+struct ZParams {
+    GemmParams g;                 // alpha / beta of g are unused
+    double ar, ai, br, bi;        // alpha, beta
+};
+
+// X = 64 (A) or 128 (B) rows of the "mn" dimension
+template <bool KMAJOR, int X, int LD_MNv>
+__device__ __forceinline__ void zload_slice(double2* s, const double2* g, int ld, int x_rem, int k_rem,
+                                            bool al16, int ptid)
+{
+    const uint32_t sbase = smem_u32(s);
+    constexpr int NELEM = X * KC;
+#pragma unroll
+    for (int i = 0; i < NELEM / (NPRODUCERS * 32); ++i) {
+        const int c = ptid + i * (NPRODUCERS * 32);
+        int row, col;
+        bool ok;
+        uint32_t soff;
+        if (!KMAJOR) {
+            row = c / X;               // kk
+            col = c % X;               // x
+            ok = (row < k_rem) && (col < x_rem);
+            soff = (uint32_t)(row * LD_MNv + col);
+        }
+        else {
+            row = c / KC;              // x
+            col = c % KC;              // kk
+            ok = (row < x_rem) && (col < k_rem);
+            soff = (uint32_t)(row * ZLD_K + col);
+        }
+        const double2* src = ok ? (g + ((int64_t)row * ld + col)) : g;
+        const uint32_t dst = sbase + soff * 16u;
+        if (al16) {
+            cp_async16(dst, src, ok ? 16 : 0);
+        }
+        else {
+            cp_async8(dst, src, ok ? 8 : 0);
+            cp_async8(dst + 8u, reinterpret_cast<const double*>(src) + 1, ok ? 8 : 0);
+        }
+    }
+}
+
+// OPA / OPB: 0 = N, 1 = T, 2 = C
+template <int OPA, int OPB, bool INL>
+__global__ void __launch_bounds__(NTHREADS, 1)
+zgemm_tiles_kernel(const __grid_constant__ ZParams zp)
+{
+    const GemmParams& p = zp.g;
+    extern __shared__ __align__(16) double smem[];
+    double2* sA = reinterpret_cast<double2*>(smem);
+    double2* sB = sA + ZSTAGES * ZSLICE_A;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sB + ZSTAGES * ZSLICE_B);
+    const uint32_t full0 = smem_u32(bars);
+    const uint32_t empty0 = smem_u32(bars + ZSTAGES);
+
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
+    const int warp = tid >> 5;
+
+    if (tid == 0) {
+        for (int s = 0; s < ZSTAGES; ++s) {
+            mbar_init(full0 + 8 * s, NPRODUCERS * 32);
+            mbar_init(empty0 + 8 * s, NCONSUMERS);
+        }
+    }
+    __syncthreads();
+
+    constexpr bool A_KMAJOR = (OPA != 0);
+    constexpr bool B_KMAJOR = (OPB == 0);
+    constexpr bool CONJ_A = (OPA == 2);
+    constexpr bool CONJ_B = (OPB == 2);
+
+    Walker<INL, ZBM> wk;
+    wk.start(p);
+    int stage = 0;
+    uint32_t phase = 0;
+
+    if (warp >= NCONSUMERS) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" :: "n"(REGS_PRODUCER));
+        const int ptid = tid - NCONSUMERS * 32;
+#pragma unroll 1
+        while (wk.valid) {
+            const Item& it = wk.it;
+            const double2* A = reinterpret_cast<const double2*>(it.a);
+            const double2* B = reinterpret_cast<const double2*>(it.b);
+            const bool a16 = (((uintptr_t)it.a) & 15) == 0, b16 = (((uintptr_t)it.b) & 15) == 0;
+#pragma unroll 1
+            for (int kc = 0; kc < wk.nk; ++kc) {
+                const int k0 = kc * KC;
+                const int k_rem = it.k - k0;
+                const double2* ga = A_KMAJOR ? A + (int64_t)it.m0 * it.lda + k0
+                                             : A + (int64_t)k0 * it.lda + it.m0;
+                const double2* gb = B_KMAJOR ? B + (int64_t)it.n0 * it.ldb + k0
+                                             : B + (int64_t)k0 * it.ldb + it.n0;
+                mbar_wait(empty0 + 8 * stage, phase ^ 1);
+                zload_slice<A_KMAJOR, ZBM, ZLD_A_MN>(sA + stage * ZSLICE_A, ga, it.lda, it.m, k_rem, a16, ptid);
+                zload_slice<B_KMAJOR, BN, ZLD_B_MN>(sB + stage * ZSLICE_B, gb, it.ldb, it.n, k_rem, b16, ptid);
+                cp_async_mbar_arrive(full0 + 8 * stage);
+                if (++stage == ZSTAGES) { stage = 0; phase ^= 1; }
+            }
+            wk.next_item(p);
+        }
+        cp_async_wait_all();
+        return;
+    }
+
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" :: "n"(REGS_CONSUMER));
+    const int g = lane >> 2;
+    const int t = lane & 3;
+    const int wm = (warp & 1) * 32;
+    const int wn = (warp >> 1) * 32;
+
+#pragma unroll 1
+    while (wk.valid) {
+        double cre[4][4][2], cim[4][4][2];
+#pragma unroll
+        for (int in = 0; in < 4; ++in)
+#pragma unroll
+            for (int im = 0; im < 4; ++im) {
+                cre[in][im][0] = cre[in][im][1] = 0.0;
+                cim[in][im][0] = cim[in][im][1] = 0.0;
+            }
+        const int nk = wk.nk;
+#pragma unroll 1
+        for (int kc = 0; kc < nk; ++kc) {
+            mbar_wait(full0 + 8 * stage, phase);
+            const double2* a_s = sA + stage * ZSLICE_A;
+            const double2* b_s = sB + stage * ZSLICE_B;
+#pragma unroll
+            for (int k4 = 0; k4 < KC / 4; ++k4) {
+                double2 af[4], bf[4];
+                const int kk = k4 * 4 + t;
+#pragma unroll
+                for (int im = 0; im < 4; ++im) {
+                    const int x = wm + im * 8 + g;
+                    af[im] = A_KMAJOR ? a_s[x * ZLD_K + kk] : a_s[kk * ZLD_A_MN + x];
+                    if (CONJ_A) af[im].y = -af[im].y;
+                }
+#pragma unroll
+                for (int in = 0; in < 4; ++in) {
+                    const int x = wn + in * 8 + g;
+                    bf[in] = B_KMAJOR ? b_s[x * ZLD_K + kk] : b_s[kk * ZLD_B_MN + x];
+                    if (CONJ_B) bf[in].y = -bf[in].y;
+                }
+#pragma unroll
+                for (int in = 0; in < 4; ++in) {
+                    const double nby = -bf[in].y;
+#pragma unroll
+                    for (int im = 0; im < 4; ++im) {
+                        dmma884(cre[in][im][0], cre[in][im][1], bf[in].x, af[im].x);
+                        dmma884(cre[in][im][0], cre[in][im][1], nby, af[im].y);
+                        dmma884(cim[in][im][0], cim[in][im][1], bf[in].x, af[im].y);
+                        dmma884(cim[in][im][0], cim[in][im][1], bf[in].y, af[im].x);
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(empty0 + 8 * stage);
+            if (++stage == ZSTAGES) { stage = 0; phase ^= 1; }
+        }
+
+        // ---- epilogue: lane owns rows (2t, 2t+1) of column g of each 8 x 8 fragment ----
+        {
+            const Item& it = wk.it;
+            const bool lower = (it.flags & TE_TILE_LOWER) != 0;
+            const bool upper = (it.flags & TE_TILE_UPPER) != 0;
+            const bool herm = (it.flags & TE_TILE_HERMITIAN) != 0;
+            const bool beta_nz = (zp.br != 0.0) || (zp.bi != 0.0);
+            const bool c16 = (((uintptr_t)it.c) & 15) == 0;
+            double2* cblk = reinterpret_cast<double2*>(it.c) + (int64_t)it.n0 * it.ldc + it.m0;
+#pragma unroll
+            for (int in = 0; in < 4; ++in) {
+                const int col = wn + in * 8 + g;
+                if (col >= it.n) continue;
+                const int gcol = it.n0 + col;
+#pragma unroll
+                for (int im = 0; im < 4; ++im) {
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const int row = wm + im * 8 + 2 * t + e;
+                        if (row >= it.m) continue;
+                        const int grow = it.m0 + row;
+                        if (lower && grow < gcol) continue;
+                        if (upper && grow > gcol) continue;
+                        const double ar = cre[in][im][e], ai = cim[in][im][e];
+                        double vr = zp.ar * ar - zp.ai * ai;
+                        double vi = zp.ar * ai + zp.ai * ar;
+                        double2* dst = cblk + (int64_t)col * it.ldc + row;
+                        if (beta_nz) {
+                            double2 old;
+                            if (c16) old = *dst;
+                            else { old.x = reinterpret_cast<double*>(dst)[0]; old.y = reinterpret_cast<double*>(dst)[1]; }
+                            vr += zp.br * old.x - zp.bi * old.y;
+                            vi += zp.br * old.y + zp.bi * old.x;
+                        }
+                        if (herm && grow == gcol) vi = 0.0;
+                        if (c16) *dst = make_double2(vr, vi);
+                        else { reinterpret_cast<double*>(dst)[0] = vr; reinterpret_cast<double*>(dst)[1] = vi; }
+                    }
+                }
+            }
+        }
+        wk.next_item(p);
+    }
+}
+
 // ---- host side ----------------------------------------------------------------
 template <bool TA, bool TB, bool INL>
 static int launch(int device, cudaStream_t stream, const GemmParams& p)
@@ -486,6 +716,82 @@ int dgemm_inline(int device, cudaStream_t stream, int opa, int opb, double alpha
     return dispatch<true>(device, stream, opa, opb, p);
 }
 
+
+template <int OPA, int OPB, bool INL>
+static int zlaunch(int device, cudaStream_t stream, const ZParams& zp)
+{
+    static bool configured[64] = {};
+    auto kern = zgemm_tiles_kernel<OPA, OPB, INL>;
+    if (device < 64 && !configured[device]) {
+        TE_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           ZSMEM_BYTES));
+        configured[device] = true;
+    }
+    const GemmParams& p = zp.g;
+    const int64_t grid = (p.total_work + p.items_per_cta - 1) / p.items_per_cta;
+    kern<<<(unsigned)grid, NTHREADS, ZSMEM_BYTES, stream>>>(zp);
+    te::count_launch();
+    TE_CUDA_CHECK(cudaGetLastError());
+    return TE_OK;
+}
+
+static int op_index(int op) { return op == TE_OP_N ? 0 : (op == TE_OP_T ? 1 : 2); }
+
+template <bool INL>
+static int zdispatch(int device, cudaStream_t stream, int opa, int opb, const ZParams& zp)
+{
+    switch (op_index(opa) * 3 + op_index(opb)) {
+        case 0: return zlaunch<0, 0, INL>(device, stream, zp);
+        case 1: return zlaunch<0, 1, INL>(device, stream, zp);
+        case 2: return zlaunch<0, 2, INL>(device, stream, zp);
+        case 3: return zlaunch<1, 0, INL>(device, stream, zp);
+        case 4: return zlaunch<1, 1, INL>(device, stream, zp);
+        case 5: return zlaunch<1, 2, INL>(device, stream, zp);
+        case 6: return zlaunch<2, 0, INL>(device, stream, zp);
+        case 7: return zlaunch<2, 1, INL>(device, stream, zp);
+        default: return zlaunch<2, 2, INL>(device, stream, zp);
+    }
+}
+
+int zgemm_batched(int device, cudaStream_t stream, int opa, int opb, const double* alpha,
+                  const double* beta, const te_tile_desc* desc, int64_t count, int32_t max_m,
+                  int32_t max_n)
+{
+    ZParams zp;
+    GemmParams& p = zp.g;
+    p.desc = desc;
+    p.nbm = (max_m + ZBM - 1) / ZBM;
+    p.nbn = (max_n + BN - 1) / BN;
+    p.total_work = count * p.nbm * p.nbn;
+    p.items_per_cta = items_per_cta(device, p.total_work);
+    p.alpha = p.beta = 0.0;
+    p.inline_count = 0;
+    zp.ar = alpha[0];  zp.ai = alpha[1];  zp.br = beta[0];  zp.bi = beta[1];
+    return zdispatch<false>(device, stream, opa, opb, zp);
+}
+
+int zgemm_inline(int device, cudaStream_t stream, int opa, int opb, const double* alpha,
+                 const double* beta, const te_tile_desc* desc_host, int count)
+{
+    ZParams zp;
+    GemmParams& p = zp.g;
+    p.desc = nullptr;
+    int32_t max_m = 0, max_n = 0;
+    for (int i = 0; i < count; ++i) {
+        p.inl[i] = desc_host[i];
+        if (desc_host[i].m > max_m) max_m = desc_host[i].m;
+        if (desc_host[i].n > max_n) max_n = desc_host[i].n;
+    }
+    p.nbm = (max_m + ZBM - 1) / ZBM;
+    p.nbn = (max_n + BN - 1) / BN;
+    p.total_work = (int64_t)count * p.nbm * p.nbn;
+    p.items_per_cta = items_per_cta(device, p.total_work);
+    p.alpha = p.beta = 0.0;
+    p.inline_count = count;
+    zp.ar = alpha[0];  zp.ai = alpha[1];  zp.br = beta[0];  zp.bi = beta[1];
+    return zdispatch<true>(device, stream, opa, opb, zp);
+}
+
 // dtype dispatch used by the C ABI and by the panel code (te_panel.cu)
 int gemm_batched_any(int device, cudaStream_t stream, int dtype, int opa, int opb,
                      const void* alpha, const void* beta, const te_tile_desc* desc,
@@ -496,7 +802,10 @@ int gemm_batched_any(int device, cudaStream_t stream, int dtype, int opa, int op
     if (dtype == TE_F64)
         return dgemm_batched(device, stream, opa, opb, *(const double*)alpha,
                              *(const double*)beta, desc, count, max_m, max_n);
-    return TE_ERR_UNSUPPORTED;
+    if (dtype == TE_C64)
+        return zgemm_batched(device, stream, opa, opb, (const double*)alpha, (const double*)beta,
+                             desc, count, max_m, max_n);
+    return TE_ERR_ARG;
 }
 
 int gemm_inline_any(int device, cudaStream_t stream, int dtype, int opa, int opb,
@@ -507,7 +816,10 @@ int gemm_inline_any(int device, cudaStream_t stream, int dtype, int opa, int opb
     if (dtype == TE_F64)
         return dgemm_inline(device, stream, opa, opb, *(const double*)alpha,
                             *(const double*)beta, desc_host, count);
-    return TE_ERR_UNSUPPORTED;
+    if (dtype == TE_C64)
+        return zgemm_inline(device, stream, opa, opb, (const double*)alpha, (const double*)beta,
+                            desc_host, count);
+    return TE_ERR_ARG;
 }
 
 }  // namespace te

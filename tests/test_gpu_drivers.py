@@ -220,3 +220,49 @@ def test_pool_returns_to_level_after_gemm(sl):
     for M in (A, B, Cm):
         avail, cap = M.pool_stats()
         assert avail == cap, (avail, cap)
+
+
+# ------------------------------ complex-FP64 drivers ------------------------------
+ZALPHA, ZBETA = ALPHA + 1.4142135623730951j, BETA + 1.7320508075688772j    # test/test.cc:392-393
+
+
+@pytest.mark.parametrize("ops", ["NN", "CN", "NT", "CC"])
+def test_zgemm_driver_vs_oracle(sl, ops):
+    """config 5 scaled down: nb = 96 with a ragged last tile in m, n and k."""
+    opa, opb = ops
+    m, n, k, nb = 500, 420, 330, 96
+    ash = (m, k) if opa == "N" else (k, m)
+    bsh = (k, n) if opb == "N" else (n, k)
+    A0 = ol.matgen(1, *ash, np.complex128)
+    B0 = ol.matgen(2, *bsh, np.complex128)
+    C0 = ol.matgen(3, m, n, np.complex128)
+    A = sl.Matrix(ash[0], ash[1], nb, dtype=np.complex128).generate(1)
+    B = sl.Matrix(bsh[0], bsh[1], nb, dtype=np.complex128).generate(2)
+    Cm = sl.Matrix(m, n, nb, dtype=np.complex128).generate(3)
+    assert np.array_equal(A.to_numpy(), A0)
+    sl.gemm(ZALPHA, A, B, ZBETA, Cm, opa, opb)
+    want = C0.copy(order="F")
+    ol.oracle().oracle_zgemm(ord(opa), ord(opb), m, n, k, nb, ol.Z(ZALPHA), ol.P(A0), ash[0], ol.P(B0),
+                             bsh[0], ol.Z(ZBETA), ol.P(want), m)
+    err = np.abs(Cm.to_numpy() - want).max() / np.abs(want).max()
+    assert err <= 3 * np.sqrt(4 * k) * EPS, err
+
+
+@pytest.mark.parametrize("uplo", "LU")
+def test_zpotrf_driver_vs_oracle(sl, uplo):
+    n, nb = 700, 96
+    A0 = ol.matgen(7, n, n, np.complex128)
+    A0[np.arange(n), np.arange(n)] += n
+    A = sl.HermitianMatrix(uplo, n, nb, dtype=np.complex128).from_numpy(A0)
+    assert sl.potrf(A) == 0
+    want = A0.copy(order="F")
+    assert ol.oracle().oracle_zpotrf(ord(uplo), n, nb, ol.P(want), n) == 0
+    tri = np.tril if uplo == "L" else np.triu
+    got = A.to_numpy()
+    assert np.abs(tri(got) - tri(want)).max() / np.abs(tri(want)).max() <= 50 * EPS
+    F = tri(got)
+    D = np.diag(A0).real
+    S = (np.tril(A0, -1) + np.tril(A0, -1).conj().T if uplo == "L"
+         else np.triu(A0, 1) + np.triu(A0, 1).conj().T) + np.diag(D)
+    R = S - (F @ F.conj().T if uplo == "L" else F.conj().T @ F)
+    assert np.linalg.norm(R) / (n * np.linalg.norm(S)) <= 50 * EPS

@@ -288,3 +288,88 @@ def test_pool_semantics(te):
     check(te.te_pool_stats(pool, C.byref(av), C.byref(cap), None))
     assert (av.value, cap.value) == (0, 0)
     check(te.te_pool_destroy(pool))
+
+
+# ------------------------------ complex-FP64 (TE_C64) ------------------------------
+@pytest.mark.parametrize("opa", "NTC")
+@pytest.mark.parametrize("opb", "NTC")
+@pytest.mark.parametrize("shape", [(80, 64, 16), (384, 384, 384), (130, 257, 37), (128, 384, 128), (1, 1, 1)])
+def test_zgemm_tiles_vs_oracle(te, opa, opb, shape):
+    m, n, k = shape
+    run_gemm(te, np.complex128, opa, opb, m, n, k, 3.141592653589793 + 1.4142135623730951j,
+             2.718281828459045 + 1.7320508075688772j)
+
+
+@pytest.mark.parametrize("inline", [False, True])
+def test_zgemm_padding_beta0_and_inline(te, inline):
+    run_gemm(te, np.complex128, "N", "C", 200, 131, 77, -1.0, 0.0, inline=inline, ld_pad=3)
+    run_gemm(te, np.complex128, "C", "N", 65, 129, 17, 0.5 - 0.25j, 1.0, inline=inline, ld_pad=1)
+
+
+@pytest.mark.parametrize("flags", [1 | 4, 2 | 4])
+def test_zherk_diagonal_tile_mask(te, flags):
+    """lower / upper mask and the herk rule: imaginary part of the diagonal set to zero"""
+    run_gemm(te, np.complex128, "N", "C", 300, 300, 64, -1.0, 1.0, flags=flags)
+
+
+@pytest.mark.parametrize("uplo", "LU")
+@pytest.mark.parametrize("n", [1, 37, 64, 200, 384])
+def test_zpotrf_tile_vs_oracle(te, uplo, n):
+    import torch
+    from slate_d35_b200 import check
+    lda = n + 1
+    full = ol.matgen(5, lda, n, np.complex128)
+    A = full[:n, :]
+    A[np.arange(n), np.arange(n)] += n
+    want = full.copy(order="F")
+    assert ol.oracle().oracle_tile_zpotrf(ord(uplo), n, ol.P(want), lda) == 0
+    dA = dev(full)
+    info = torch.full((1,), 7, dtype=torch.int32, device="cuda")
+    sb = te.te_potrf_scratch_bytes(1)
+    scratch = torch.empty(sb, dtype=torch.uint8, device="cuda")
+    check(te.te_potrf_tile(0, stream(), 1, ord(uplo), n, dA.data_ptr(), lda, info.data_ptr(),
+                           scratch.data_ptr(), sb))
+    got = host(dA, (lda, n), np.complex128)
+    assert int(info.item()) == 0
+    tri = np.tril if uplo == "L" else np.triu
+    # LAPACK leaves the imaginary part of the input diagonal unreferenced; compare the factor
+    assert np.abs(tri(got[:n]) - tri(want[:n])).max() / np.abs(tri(want[:n])).max() <= 50 * EPS
+    other = (lambda x: np.triu(x[:n], 1)) if uplo == "L" else (lambda x: np.tril(x[:n], -1))
+    assert np.array_equal(other(got), other(full))
+
+
+@pytest.mark.parametrize("side,uplo,op,diag", [
+    ("R", "L", "C", "N"), ("R", "U", "T", "N"), ("L", "L", "N", "U"), ("L", "U", "C", "N")])
+def test_ztrsm_batched_vs_oracle(te, side, uplo, op, diag):
+    import torch
+    from slate_d35_b200 import TrsmDesc, check
+    na, count = 384, 2
+    lda = na + 1
+    Afull = ol.matgen(16, lda, na, np.complex128, dist=2)
+    Afull[np.arange(na), np.arange(na)] += na ** 0.5 * 2
+    dA = dev(Afull)
+    descs = (TrsmDesc * count)()
+    keep, cases = [], []
+    for t, sz in enumerate((na, 70)):
+        m, n = (sz, na) if side == "R" else (na, sz)
+        B = ol.matgen(40 + t, m, n, np.complex128, dist=2)
+        dB = dev(B)
+        keep.append(dB)
+        descs[t].b, descs[t].m, descs[t].n, descs[t].ldb = dB.data_ptr(), m, n, m
+        cases.append((B, dB, m, n))
+    dd = torch.frombuffer(bytearray(bytes(descs)), dtype=torch.uint8).cuda()
+    sb = te.te_trsm_scratch_bytes(1, na, count)
+    scratch = torch.empty(sb, dtype=torch.uint8, device="cuda")
+    alpha = 0.75 - 0.5j
+    check(te.te_trsm_batched(0, stream(), 1, ord(side), ord(uplo), ord(op), ord(diag),
+                             scalar(alpha, np.complex128), dA.data_ptr(), lda, na, dd.data_ptr(),
+                             count, max(c[2] for c in cases), max(c[3] for c in cases),
+                             scratch.data_ptr(), sb))
+    torch.cuda.synchronize()
+    for B, dB, m, n in cases:
+        want = B.copy(order="F")
+        ol.oracle().oracle_tile_ztrsm(ord(side), ord(uplo), ord(op), ord(diag), m, n, ol.Z(alpha),
+                                      ol.P(Afull), lda, ol.P(want), m)
+        got = host(dB, (m, n), np.complex128)
+        err = np.abs(got - want).max() / np.abs(want).max()
+        assert err <= 50 * EPS * np.sqrt(na), (err, side, uplo, op, diag)
