@@ -57,6 +57,9 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--potrf-n", type=int, default=N_POTRF)
     ap.add_argument("--lookahead", type=int, default=1)
+    ap.add_argument("--zgemm", action="store_true",
+                    help="also run config 5: slate::gemm complex<double> n=32768 nb=384 (ragged tiles)")
+    ap.add_argument("--zgemm-n", type=int, default=32768)
     return ap.parse_args()
 
 
@@ -344,6 +347,50 @@ def main():
             potrf["backward_error_bound_50eps"] = 50 * 2.0 ** -52
         H.free()
 
+    # ---- zgemm, BASELINE.json configs[4]: complex<double>, nb = 384, ragged last tiles -------
+    zg = None
+    if args.zgemm:
+        nz, nbz = args.zgemm_n, 384
+        za, zb = ALPHA + 1.4142135623730951j, BETA + 1.7320508075688772j
+        Az = sl.Matrix(nz, nz, nbz, p, q, dtype=np.complex128).generate(1)
+        Bz = sl.Matrix(nz, nz, nbz, p, q, dtype=np.complex128).generate(2)
+        Cz = sl.Matrix(nz, nz, nbz, p, q, dtype=np.complex128).generate(3)
+        Aw = sl.Matrix(nz, 2 * nbz, nbz, p, q, dtype=np.complex128).generate(4)
+        Bw = sl.Matrix(2 * nbz, nz, nbz, p, q, dtype=np.complex128).generate(5)
+        sl.gemm(za, Aw, Bw, zb, Cz, lookahead=args.lookahead)
+        Aw.free()
+        Bw.free()
+        Cz.generate(3)
+        barrier()
+        ms_z = sl.gemm(za, Az, Bz, zb, Cz, lookahead=args.lookahead, timed=True)
+        barrier()
+        ms_z = max_over_ranks(ms_z)
+        # tester check with X of kind rand (complex): ||C X - (alpha A (B X) + beta C0 X)||_1 / ||Y||_1
+        Xz = sl.Matrix(nz, 10, nbz, p, q, dtype=np.complex128).generate(6)
+        Wz = sl.Matrix(nz, 10, nbz, p, q, dtype=np.complex128)
+        Yz = sl.Matrix(nz, 10, nbz, p, q, dtype=np.complex128)
+        Zz = sl.Matrix(nz, 10, nbz, p, q, dtype=np.complex128)
+        sl.gemm(1.0, Bz, Xz, 0.0, Wz)
+        sl.gemm(za, Az, Wz, 0.0, Yz)
+        sl.gemm(1.0, Cz, Xz, 0.0, Zz)
+        Cz.generate(3)
+        sl.gemm(zb, Cz, Xz, 1.0, Yz)
+        yh, zh = Yz.to_numpy(), Zz.to_numpy()
+        if world > 1:
+            t = torch.from_numpy(np.ascontiguousarray(np.stack([yh, zh]))).cuda()
+            t = torch.view_as_real(t).contiguous()
+            dist.all_reduce(t)
+            t = torch.view_as_complex(t)
+            yh, zh = t[0].cpu().numpy(), t[1].cpu().numpy()
+        zerr = float(np.abs(zh - yh).sum(axis=0).max() / np.abs(yh).sum(axis=0).max())
+        fz = 8.0 * nz ** 3
+        zg = {"metric": "zgemm FP64 TFLOP/s (slate::gemm complex<double>)", "n": nz, "nb": nbz,
+              "ms": ms_z, "value": fz / (ms_z * 1e-3) * 1e-12, "unit": "TFLOP/s",
+              "frac_of_fp64_tensor_peak": fz / (ms_z * 1e-3) * 1e-12 / (peak_tf * world),
+              "error": zerr, "error_bound": 3 * 2.0 ** -52 * 2 * 2 ** 0.5}
+        for M in (Az, Bz, Cz, Xz, Wz, Yz, Zz):
+            M.free()
+
     # ---- CPU baseline: the reference's HostTask path on the host cores --------------------
     cpu = None
     if not args.no_cpu and rank == 0 and world == 1:
@@ -384,7 +431,7 @@ def main():
                          "traffic": traffic, "kernel": "dgemm_tiles_kernel",
                          "peak_source": "measured in this run by te_peak_fp64 (register-resident "
                                         "DMMA.8x8x4); MEASURED_PEAKS.json has no FP64 entry"},
-            "e2e": e2e, "cpu_baseline": cpu, "potrf": potrf,
+            "e2e": e2e, "cpu_baseline": cpu, "potrf": potrf, "zgemm": zg,
         }
         print(json.dumps(line), flush=True)
     sl.finalize()
