@@ -336,7 +336,8 @@ def main():
         potrf = {"metric": "dpotrf FP64 TFLOP/s (slate::potrf)", "n": npo, "nb": nb,
                  "lookahead": args.lookahead, "info": int(info), "ms": ms_p,
                  "value": pf / (ms_p * 1e-3) * 1e-12, "unit": "TFLOP/s",
-                 "frac_of_dmma_peak": pf / (ms_p * 1e-3) * 1e-12 / peak_tf, "gpu_launches": int(lp)}
+                 "frac_of_fp64_tensor_peak": pf / (ms_p * 1e-3) * 1e-12 / (peak_tf * world),
+                 "gpu_launches": int(lp)}
         if npo <= 32768:
             r, a0 = sl.potrf_residual(H, 7, True)
             if world > 1:

@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <string>
 
 namespace slate {
 
@@ -454,12 +455,24 @@ void Engine::trace_dump(const char* title)
     sync_all();
     std::fprintf(stderr, "[slate_b200 rank %d] %s: %zu launches (start ms, duration ms, host enqueue ms)\n",
                  comm_world()->rank, title, trace_.size());
+    // SLATE_B200_TRACE_FILE=<prefix>: every record, one file per rank and call
+    std::FILE* tf = nullptr;
+    if (const char* prefix = std::getenv("SLATE_B200_TRACE_FILE")) {
+        static int call = 0;
+        std::string name = std::string(prefix) + "_r" + std::to_string(comm_world()->rank) + "_"
+                           + std::to_string(call++) + ".txt";
+        tf = std::fopen(name.c_str(), "w");
+        if (tf) std::fprintf(tf, "# %s: queue what count start_ms dur_ms host_ms\n", title);
+    }
     double h0 = trace_.front().host_s;
     size_t shown = 0;
     for (size_t i = 0; i < trace_.size(); ++i) {
         float t0 = 0, dt = 0;
         te_event_elapsed_ms(trace_epoch_, trace_[i].e0, &t0);
         te_event_elapsed_ms(trace_[i].e0, trace_[i].e1, &dt);
+        if (tf)
+            std::fprintf(tf, "%d %s %lld %.3f %.3f %.3f\n", trace_[i].q, trace_[i].what,
+                         (long long)trace_[i].count, t0, dt, (trace_[i].host_s - h0) * 1e3);
         if (i < 40 || i + 4 >= trace_.size()) {
             std::fprintf(stderr, "   q%d %-10s n=%-6lld start %9.3f  dur %8.3f  host %9.3f\n", trace_[i].q,
                          trace_[i].what, (long long)trace_[i].count, t0, dt, (trace_[i].host_s - h0) * 1e3);
@@ -468,6 +481,7 @@ void Engine::trace_dump(const char* title)
         te_event_destroy(trace_[i].e0);
         te_event_destroy(trace_[i].e1);
     }
+    if (tf) std::fclose(tf);
     te_event_destroy(trace_epoch_);
     trace_epoch_ = nullptr;
     trace_.clear();
