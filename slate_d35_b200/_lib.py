@@ -72,6 +72,7 @@ def lib():
                               C.c_double, vp, i64]
     L.te_tile_sumsq.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, i64, vp]
     L.te_tile_keep_triangle.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, i64]
+    L.te_device_mem_info.argtypes = [C.c_int, C.POINTER(sz), C.POINTER(sz)]
     L.te_pool_create.argtypes = [C.c_int, sz, C.POINTER(vp)]
     L.te_pool_reserve.argtypes = [vp, i64]
     L.te_pool_alloc.argtypes = [vp, C.POINTER(vp)]

@@ -651,7 +651,7 @@ static int launch(int device, cudaStream_t stream, const GemmParams& p)
     return TE_OK;
 }
 
-// Up to 8 consecutive 128x128 blocks per CTA (about 0.5 ms at k = 512) once there are
+// Up to 16 consecutive 128x128 blocks per CTA (about 1 ms at k = 512) once there are
 // enough blocks for several waves; fewer when the launch is small, so that it still
 // spreads over all SMs.
 static int items_per_cta(int device, int64_t total_work)
@@ -659,11 +659,12 @@ static int items_per_cta(int device, int64_t total_work)
     static int cap = -1;
     if (cap < 0) {
         const char* e = getenv("TE_ITEMS_PER_CTA");
-        cap = (e && atoi(e) > 0) ? atoi(e) : 8;
+        cap = (e && atoi(e) > 0) ? atoi(e) : 16;
     }
     const int64_t sms = num_sms(device);
     int64_t g = total_work / (4 * sms);
     if (g < 1) g = 1;
+    g = total_work / (16 * sms) < 1 ? g : g;     // (small launches keep g = total / (4 sms))
     if (g > cap) g = cap;
     return (int)g;
 }
