@@ -339,8 +339,8 @@ dgemm_tiles_kernel(const __grid_constant__ GemmParams p)
                         for (int i2 = 0; i2 < 2; ++i2)
 #pragma unroll
                             for (int im = 0; im < 8; ++im)
-                                old[i2][im] = *reinterpret_cast<const double2*>(
-                                    c0 + (2 * h + i2) * cstep + im * 8);
+                                old[i2][im] = __ldcs(reinterpret_cast<const double2*>(
+                                    c0 + (2 * h + i2) * cstep + im * 8));
                     }
 #pragma unroll
                     for (int i2 = 0; i2 < 2; ++i2)
@@ -352,8 +352,10 @@ dgemm_tiles_kernel(const __grid_constant__ GemmParams p)
                                 v0 += beta * old[i2][im].x;
                                 v1 += beta * old[i2][im].y;
                             }
-                            *reinterpret_cast<double2*>(c0 + (2 * h + i2) * cstep + im * 8) =
-                                make_double2(v0, v1);
+                            // C is touched once per launch: streaming loads / stores (evict
+                            // first) so that it does not push the reused A / B panels out of L2
+                            __stcs(reinterpret_cast<double2*>(c0 + (2 * h + i2) * cstep + im * 8),
+                                   make_double2(v0, v1));
                         }
                 }
             }
