@@ -60,6 +60,9 @@ def parse():
     ap.add_argument("--zgemm", action="store_true",
                     help="also run config 5: slate::gemm complex<double> n=32768 nb=384 (ragged tiles)")
     ap.add_argument("--zgemm-n", type=int, default=32768)
+    ap.add_argument("--herk", action="store_true",
+                    help="also run config 4: one internal::herk / syrk tile update, k = nb = 512")
+    ap.add_argument("--herk-n", type=int, default=32768)
     return ap.parse_args()
 
 
@@ -397,6 +400,32 @@ def main():
         for M in (Az, Bz, Cz, Xz, Wz, Yz, Zz):
             M.free()
 
+    # ---- herk / syrk tile-update microbench, BASELINE.json configs[3] (1 GPU) ---------------
+    hk = None
+    if args.herk and world == 1:
+        nh = args.herk_n
+        Ah = sl.Matrix(nh, nb, nb).generate(1, dist=2)
+        hk = {"n": nh, "k": nb, "nb": nb, "flops": "k*n*(n+1) (blaspp flops.hh:128-132)"}
+        for name, cls, fn in (("herk", sl.HermitianMatrix, lambda Cx: sl.internal_herk(-1.0, Ah, 1.0, Cx)),
+                              ("syrk", sl.SymmetricMatrix, lambda Cx: sl.internal_syrk(-1.0, Ah, 1.0, Cx))):
+            Ch = cls("L", nh, nb).generate(2)
+            best = None
+            for rep in range(5):
+                sl.sync()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                # the engine's queue 0 is its own stream: bracket with full syncs
+                t0 = time.perf_counter()
+                fn(Ch)
+                sl.sync()
+                dt = time.perf_counter() - t0
+                if rep >= 2:
+                    best = dt if best is None else min(best, dt)
+            hk[name] = {"ms": best * 1e3, "value": nb * nh * (nh + 1.0) / best * 1e-12, "unit": "TFLOP/s",
+                        "frac_of_fp64_tensor_peak": nb * nh * (nh + 1.0) / best * 1e-12 / peak_tf,
+                        "timing": "host wall clock around one call + sync (one launch of ~2080 tiles)"}
+            Ch.free()
+        Ah.free()
+
     # ---- CPU baseline: the reference's HostTask path on the host cores --------------------
     cpu = None
     if not args.no_cpu and rank == 0 and world == 1:
@@ -437,7 +466,7 @@ def main():
                          "traffic": traffic, "kernel": "dgemm_tiles_kernel",
                          "peak_source": "measured in this run by te_peak_fp64 (register-resident "
                                         "DMMA.8x8x4); MEASURED_PEAKS.json has no FP64 entry"},
-            "e2e": e2e, "cpu_baseline": cpu, "potrf": potrf, "zgemm": zg,
+            "e2e": e2e, "cpu_baseline": cpu, "potrf": potrf, "zgemm": zg, "herk_microbench": hk,
         }
         print(json.dumps(line), flush=True)
     sl.finalize()
