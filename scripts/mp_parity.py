@@ -82,6 +82,41 @@ def main():
                     print(f"potrf {p}x{q} la={la} {uplo}: info {info} err {err:.2e} backward {berr:.2e} "
                           f"{'ok' if ok else 'FAIL'}", flush=True)
                 H.free()
+    # host-origin matrices in ScaLAPACK layout (the e2e path of bench.py): every rank passes its
+    # own 2D block-cyclic local array, tiles are staged H2D / D2H around the broadcasts
+    for (p, q) in GRIDS[world]:
+        m, n, k, nb = 1500, 1300, 1100, 256
+        myrow, mycol = rank % p, rank // p
+
+        def local_of(full, rows, cols):
+            ri = [i for t in range(myrow, -(-rows // nb), p) for i in range(t * nb, min((t + 1) * nb, rows))]
+            ci = [j for t in range(mycol, -(-cols // nb), q) for j in range(t * nb, min((t + 1) * nb, cols))]
+            return np.asfortranarray(full[np.ix_(ri, ci)]), ri, ci
+
+        A0, B0, C0 = ol.matgen(1, m, k), ol.matgen(2, k, n), ol.matgen(3, m, n)
+        Al, _, _ = local_of(A0, m, k)
+        Bl, _, _ = local_of(B0, k, n)
+        Cl, ri, ci = local_of(C0, m, n)
+        if Al.size and Bl.size and Cl.size:
+            A = sl.Matrix.fromScaLAPACK(m, k, Al, nb, p, q)
+            B = sl.Matrix.fromScaLAPACK(k, n, Bl, nb, p, q)
+            Cm = sl.Matrix.fromScaLAPACK(m, n, Cl, nb, p, q)
+            sl.gemm(3.141592653589793, A, B, 2.718281828459045, Cm)
+            full = np.zeros((m, n))
+            full[np.ix_(ri, ci)] = Cl
+            t = torch.from_numpy(full).cuda()
+            dist.all_reduce(t)
+            if rank == 0:
+                want = C0.copy(order="F")
+                ol.oracle().oracle_dgemm(ord("N"), ord("N"), m, n, k, nb, 3.141592653589793, ol.P(A0), m,
+                                         ol.P(B0), k, 2.718281828459045, ol.P(want), m)
+                err = np.abs(t.cpu().numpy() - want).max() / np.abs(want).max()
+                ok = err <= 3 * np.sqrt(k) * EPS
+                fails += (not ok)
+                print(f"gemm  {p}x{q} fromScaLAPACK host buffers: err {err:.2e} {'ok' if ok else 'FAIL'}", flush=True)
+            for M in (A, B, Cm):
+                M.free()
+
     # info must be the same on every rank
     n, nb = 1200, 256
     p, q = GRIDS[world][0]
