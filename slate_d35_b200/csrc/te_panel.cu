@@ -38,6 +38,8 @@ template <> struct PanelCfg<zd>     { static constexpr int IB = 64; };
 // One CTA.  Works on the n x n (n <= IB) triangular block at A (uplo given by
 // `upper`), held in shared memory as a LOWER matrix S (an upper block is loaded
 // conjugate-transposed and stored back the same way).
+//   do_potf2 == 2: as 1 but the inverse is not formed (last diagonal block of a tile:
+//                  nothing below it needs it)
 //   do_potf2 != 0: S <- chol(S); failure at local pivot j sets *info = info_base + j + 1
 //                  (first failure wins; a non-zero *info on entry skips the block).
 //   always:        inv <- inverse of the triangular factor, dense IB-strided block in
@@ -172,6 +174,8 @@ potf2_trtri_kernel(T* A, int lda, int upper, T* inv, int* info, int info_base,
     // in registers.  Step l: x_l = -s_l / S[l][l] comes from the lane that owns row l
     // (shuffle), then every lane adds S[i][l] x_l to its rows below l: 32 independent
     // LDS + FMA per step and no barrier at all.
+    const bool want_inv = (do_potf2 != 2);
+    if (want_inv)
     for (int i = tid; i < n; i += PANEL_THREADS) {
         if (unit_diag) xd[i] = from_real<T>(1.0);
         else {
@@ -182,7 +186,7 @@ potf2_trtri_kernel(T* A, int lda, int upper, T* inv, int* info, int info_base,
         }
     }
     __syncthreads();
-    {
+    if (want_inv) {
         constexpr int MP = IB / 4;                  // rows per lane
         const int j = tid >> 2, part = tid & 3;
         if (j < IB) {                               // warps past the last column are idle
@@ -240,6 +244,7 @@ potf2_trtri_kernel(T* A, int lda, int upper, T* inv, int* info, int info_base,
             if (!upper) { if (r >= c) A[r + (int64_t)c * lda] = S[r * LD + c]; }
             else        { if (r <= c) A[r + (int64_t)c * lda] = conj_(S[c * LD + r]); }
         }
+        if (!want_inv) continue;
         // inverse, dense block with leading dimension IB
         T v = zero_<T>();
         if (!upper) {
@@ -288,11 +293,11 @@ static int potrf_tile(int device, cudaStream_t stream, int dtype, int uplo, int 
     for (int jb = 0; jb < n; jb += IB) {
         const int ib = (n - jb < IB) ? n - jb : IB;
         T* Ajj = A + jb + (int64_t)jb * lda;
+        const int rem = n - jb - ib;
         potf2_trtri_kernel<T, IB><<<1, PANEL_THREADS, panel_smem_bytes<T>(), stream>>>(
-            Ajj, lda, upper, scratch, info, jb, 1, 0, 0, 0, ib);
+            Ajj, lda, upper, scratch, info, jb, rem > 0 ? 1 : 2, 0, 0, 0, ib);
         te::count_launch();
         TE_CUDA_CHECK(cudaGetLastError());
-        const int rem = n - jb - ib;
         if (rem <= 0) break;
         te_tile_desc d;
         d.reserved = 0;
