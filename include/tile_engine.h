@@ -90,6 +90,10 @@ int te_memcpy_async(void* dst, const void* src, size_t bytes, int kind, void* st
 int te_memcpy2d_async(void* dst, size_t dpitch, const void* src, size_t spitch,
                       size_t width_bytes, size_t height, int kind, void* stream);
 int te_memset_async(void* dst, int value, size_t bytes, void* stream);
+/* Copy of a small PINNED host buffer (te_host_alloc_pinned; both pointers 16-byte aligned,
+ * sizes rounded up to 16 bytes) to the device by a kernel on `stream`, so that it does not
+ * queue on the copy engine behind bulk transfers of other streams.  For descriptor arrays. */
+int te_upload_small(int device, void* stream, void* dst_dev, const void* src_pinned, size_t bytes);
 
 /* ------------------------------------------------------------------------
  * Device-tile memory pool: fixed-size blocks (sizeof(T)*mb*nb, rounded up to

@@ -124,7 +124,7 @@ extern "C" int te_device_mem_info(int device, size_t* free_bytes, size_t* total_
 extern "C" int te_host_alloc_pinned(size_t bytes, void** ptr)
 {
     if (!ptr) return TE_ERR_ARG;
-    TE_CUDA_CHECK(cudaHostAlloc(ptr, bytes, cudaHostAllocPortable));
+    TE_CUDA_CHECK(cudaHostAlloc(ptr, bytes, cudaHostAllocPortable | cudaHostAllocMapped));
     return TE_OK;
 }
 
@@ -284,4 +284,38 @@ extern "C" int te_event_query_done(void* event)
     if (e == cudaErrorNotReady) return 0;
     te::set_last_error("cudaEventQuery", cudaGetErrorString(e));
     return -1;
+}
+
+// ---------------------------------------------------------------- small uploads by kernel
+// A descriptor array (a few hundred KB) copied with cudaMemcpyAsync queues on the host-to-
+// device copy engine BEHIND whatever bulk tile traffic another stream has already submitted
+// (measured: the launch that needed it sat idle for ~65 ms behind a 4 GiB slab of C).  This
+// copy is done by a kernel instead: it reads the pinned host buffer directly over PCIe
+// (pinned allocations are device-accessible under unified addressing) and is ordered only by
+// its own stream.
+namespace te {
+__global__ void upload_small_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src, size_t n16)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16;
+         i += (size_t)gridDim.x * blockDim.x)
+        dst[i] = src[i];
+}
+}  // namespace te
+
+extern "C" int te_upload_small(int device, void* stream, void* dst_dev, const void* src_pinned,
+                               size_t bytes)
+{
+    if (bytes == 0) return TE_OK;
+    if (!dst_dev || !src_pinned || (((uintptr_t)dst_dev | (uintptr_t)src_pinned) & 15))
+        return TE_ERR_ARG;
+    int st = te::set_device(device);
+    if (st != TE_OK) return st;
+    const size_t n16 = (bytes + 15) / 16;      // buffers are allocated with slack
+    int blocks = (int)((n16 + 255) / 256);
+    if (blocks > 64) blocks = 64;
+    te::upload_small_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((uint4*)dst_dev,
+                                                                     (const uint4*)src_pinned, n16);
+    te::count_launch();
+    TE_CUDA_CHECK(cudaGetLastError());
+    return TE_OK;
 }

@@ -243,6 +243,15 @@ public:
         updateOrigin(i, j);
         finishHostCopies();
     }
+    /// Same, but only enqueues the copies to the host (each behind the launch that produced
+    /// its tile); a later tileUpdateAllOrigin() / Engine::sync_all() completes them.
+    void tileUpdateAllOriginAsync()
+    {
+        for (int64_t j = 0; j < nt(); ++j)
+            for (int64_t i = 0; i < mt(); ++i)
+                if (tileIsLocal(i, j) && inStoredTriangle(i, j) && tileExists(i, j)) updateOrigin(i, j);
+        host_copies_pending_ = false;
+    }
     void tileUpdateAllOrigin()
     {
         for (int64_t j = 0; j < nt(); ++j)

@@ -35,6 +35,14 @@ void gemm(scalar_t alpha, Matrix<scalar_t>&& A, Matrix<scalar_t>&& B, scalar_t b
     gemm(TargetType<Target::Devices>(), alpha, A, B, beta, C, layout, priority, queue_index);
 }
 
+/// one block outer product of a multi-part launch (gemm_multi)
+template <typename scalar_t>
+struct GemmPart { Matrix<scalar_t> A, B, C; };
+
+template <typename scalar_t>
+void gemm_multi(TargetType<Target::Devices>, scalar_t alpha, std::vector<GemmPart<scalar_t>>& parts,
+                scalar_t beta, Layout layout, int64_t queue_index);
+
 // ---- herk: C = alpha A A^H + beta C on the lower triangle of C ---------------------------
 template <typename scalar_t>
 void herk(TargetType<Target::Devices>, real_type<scalar_t> alpha, Matrix<scalar_t>& A,

@@ -90,14 +90,41 @@ void gemm(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t bet
     // src/gemmC.cc:57-60
     C.allocateBatchArrays();
     C.reserveDeviceWorkspace(0);
-    A.ensureDeviceWorkspace((lookahead + 3) * A.mt());
-    B.ensureDeviceWorkspace((lookahead + 3) * B.nt());
 
-    // fetch_C (src/gemmC.cc:70-74)
-    C.tileGetAllForWritingOnDevices(LayoutConvert(layout), queue_0);
+    // Device-origin C: one launch per block step, as the reference.
+    // Host-origin C (tiles staged over PCIe): C is cut into NSLAB slabs of block columns and
+    // slab s runs its k loop `skew` steps behind slab s-1, all slabs that are active in an
+    // iteration sharing one launch.  Slab 0 starts as soon as it has arrived and the others
+    // are fetched behind the compute of the earlier ones; at the end slab s is written back
+    // while the later slabs still compute.  The reference fetches all of C before the first
+    // step and copies it back after the last (src/gemmC.cc:70-74, 187-190), which leaves
+    // both transfers exposed (2 x 0.7 s for n = 65536 on one GPU).
+    const bool staged = (C.origin() != Target::Devices) && C.num_devices() > 0;
+    const int64_t nslab = staged ? std::max<int64_t>(1, std::min<int64_t>(8, C.nt())) : 1;
+    auto slab_cols = [&](int64_t s, int64_t* j1, int64_t* j2) {
+        *j1 = s * C.nt() / nslab;
+        *j2 = (s + 1) * C.nt() / nslab - 1;
+    };
+    int64_t skew = 0;
+    if (nslab > 1) {
+        // steps of compute that cover the transfer of all of C: local bytes over ~45 GB/s of
+        // PCIe against local flops per step at ~30 TFLOP/s
+        double local_tiles = (double)C.getMaxDeviceTiles(0);
+        double bytes = local_tiles * sizeof(scalar_t) * C.tileMb(0) * C.tileNb(0);
+        double flops_step = local_tiles * 2.0 * C.tileMb(0) * C.tileNb(0) * A.tileNb(0)
+                            * (is_complex<scalar_t>::value ? 4.0 : 1.0);
+        double steps = (bytes / 45e9) / (flops_step / 30e12);
+        skew = std::max<int64_t>(1, std::min<int64_t>((int64_t)std::ceil(steps * 1.25), 16));
+    }
+    const int64_t extra_panels = skew * (nslab - 1);
+
+    // src/gemmC.cc:57-60 (panels stay resident until the last slab has used them)
+    A.ensureDeviceWorkspace((lookahead + 3 + extra_panels) * A.mt());
+    B.ensureDeviceWorkspace((lookahead + 3 + extra_panels) * B.nt());
 
     if (kt == 0) {
         // nothing to accumulate; the reference's loop does not run either
+        C.tileGetAllForWritingOnDevices(LayoutConvert(layout), queue_0);
         C.tileUpdateAllOrigin();
         Engine::instance().sync_all();
         return;
@@ -111,34 +138,79 @@ void gemm(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t bet
         BcastListTag list_B = gemm_bcast_list(1, A, B, C, k);
         B.template listBcastMT<Target::Devices>(list_B, layout);
     };
+    // fetch_C (src/gemmC.cc:70-74), one slab; the consuming launch waits for its own tiles
+    int64_t next_fetch = 0;
+    auto fetch_slabs_upto = [&](int64_t s_last) {
+        for (; next_fetch <= s_last && next_fetch < nslab; ++next_fetch) {
+            int64_t j1, j2;
+            slab_cols(next_fetch, &j1, &j2);
+            C.sub(0, C.mt() - 1, j1, j2).tileGetAllForWritingOnDevices(LayoutConvert(layout), -1);
+        }
+    };
 
     HostTimer ht;
     ht.start();
-    for (int64_t k = 0; k <= lookahead && k < kt; ++k)
+    bcast(0);
+    fetch_slabs_upto(nslab > 1 ? 1 : 0);
+    for (int64_t k = 1; k <= lookahead && k < kt; ++k)
         bcast(k);
     ht.stop(0);
 
-    for (int64_t k = 0; k < kt; ++k) {
+    const int64_t iterations = kt + extra_panels;
+    for (int64_t t = 0; t < iterations; ++t) {
         ht.start();
-        if (k > 0 && k + lookahead < kt)
-            bcast(k + lookahead);
+        if (t > 0 && t + lookahead < kt)
+            bcast(t + lookahead);
+        // slab s is first used in iteration skew * s: ask for it one slab period earlier
+        if (nslab > 1)
+            fetch_slabs_upto(t / skew + 1);
         ht.stop(0);
         ht.start();
 
-        // src/gemmC.cc:113-171: beta only on the first block outer product
-        internal::gemm<Target::Devices>(
-            alpha, A.sub(0, A.mt() - 1, k, k), B.sub(k, k, 0, B.nt() - 1),
-            k == 0 ? beta : one, std::move(C), layout, 0, queue_0);
+        // src/gemmC.cc:113-171: beta only on the first block outer product of a slab
+        if (nslab == 1) {
+            internal::gemm<Target::Devices>(
+                alpha, A.sub(0, A.mt() - 1, t, t), B.sub(t, t, 0, B.nt() - 1),
+                t == 0 ? beta : one, std::move(C), layout, 0, queue_0);
+        }
+        else {
+            std::vector<internal::GemmPart<scalar_t>> first, rest;
+            for (int64_t s = 0; s < nslab; ++s) {
+                const int64_t k = t - skew * s;
+                if (k < 0 || k >= kt) continue;
+                int64_t j1, j2;
+                slab_cols(s, &j1, &j2);
+                internal::GemmPart<scalar_t> part{A.sub(0, A.mt() - 1, k, k), B.sub(k, k, j1, j2),
+                                                  C.sub(0, C.mt() - 1, j1, j2)};
+                (k == 0 ? first : rest).push_back(part);
+            }
+            internal::gemm_multi(internal::TargetType<Target::Devices>(), alpha, first, beta, layout,
+                                 queue_0);
+            internal::gemm_multi(internal::TargetType<Target::Devices>(), alpha, rest, one, layout,
+                                 queue_0);
+            // a slab that has just had its last update goes home behind that launch
+            for (int64_t s = 0; s < nslab; ++s) {
+                if (t - skew * s == kt - 1) {
+                    int64_t j1, j2;
+                    slab_cols(s, &j1, &j2);
+                    C.sub(0, C.mt() - 1, j1, j2).tileUpdateAllOriginAsync();
+                }
+            }
+        }
         ht.stop(1);
         ht.start();
 
-        // src/gemmC.cc:173-185: drop the panel (returns to the pool when the update is done)
-        auto A_panel = A.sub(0, A.mt() - 1, k, k);
-        A_panel.releaseRemoteWorkspace();
-        A_panel.releaseLocalWorkspace();
-        auto B_panel = B.sub(k, k, 0, B.nt() - 1);
-        B_panel.releaseRemoteWorkspace();
-        B_panel.releaseLocalWorkspace();
+        // src/gemmC.cc:173-185: drop the panel the last slab has just used (its blocks return
+        // to the pool when the update is done)
+        const int64_t kr = t - extra_panels;
+        if (kr >= 0) {
+            auto A_panel = A.sub(0, A.mt() - 1, kr, kr);
+            A_panel.releaseRemoteWorkspace();
+            A_panel.releaseLocalWorkspace();
+            auto B_panel = B.sub(kr, kr, 0, B.nt() - 1);
+            B_panel.releaseRemoteWorkspace();
+            B_panel.releaseLocalWorkspace();
+        }
         Engine::instance().poll_deferred();
         ht.stop(2);
     }

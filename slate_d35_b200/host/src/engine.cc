@@ -270,6 +270,7 @@ Engine::DescSlot& Engine::acquire_desc(int q, size_t bytes)
         if (s.host) slate_te_call(te_host_free_pinned(s.host));
         if (s.dev) slate_te_call(te_device_free(device_, s.dev));
         size_t cap = bytes + bytes / 4 + 4096;
+        cap = (cap + 255) & ~(size_t)255;
         slate_te_call(te_host_alloc_pinned(cap, &s.host));
         slate_te_call(te_device_malloc(device_, cap, &s.dev));
         s.capacity = cap;
@@ -280,7 +281,8 @@ Engine::DescSlot& Engine::acquire_desc(int q, size_t bytes)
 
 void Engine::upload_desc(int q, DescSlot& s, size_t bytes)
 {
-    slate_te_call(te_memcpy_async(s.dev, s.host, bytes, TE_COPY_H2D, compute_stream(q)));
+    // by kernel, not by the copy engine: see te_upload_small
+    slate_te_call(te_upload_small(device_, compute_stream(q), s.dev, s.host, bytes));
 }
 
 void Engine::retire_desc(int q, DescSlot& s)

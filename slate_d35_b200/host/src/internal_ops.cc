@@ -83,35 +83,14 @@ Op trans_of(Op op, bool* ok)
 
 }  // namespace
 
-//------------------------------------------------------------------------------
+namespace {
+/// Fetches the local tiles of one block outer product onto the device (queue q) and appends
+/// their descriptors, in 8 x 8 super-blocks, to `batch`.
 template <typename scalar_t>
-void gemm(TargetType<Target::Devices>, scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B,
-          scalar_t beta, Matrix<scalar_t>& C, Layout layout, int priority, int64_t queue_index)
+void append_gemm_tiles(DescBatch& batch, Matrix<scalar_t>& A, Matrix<scalar_t>& B, Matrix<scalar_t>& C,
+                       Layout layout, int q)
 {
-    slate_assert(layout == Layout::ColMajor);
-    slate_assert(C.mt() > 0 && C.nt() > 0);
-    slate_assert(A.nt() == 1 && B.mt() == 1);
-    slate_assert(A.mt() == C.mt() && B.nt() == C.nt());
-    slate_assert(C.num_devices() > 0);
     const int device = 0;
-    const int q = (int)queue_index;
-
-    // src/internal/internal_gemm.cc:383-414: if op(C) is not NoTrans, compute the
-    // transposed product on the stored tiles.
-    Op opA = A.op(), opB = B.op();
-    if (C.op() != Op::NoTrans) {
-        if (opA == Op::NoTrans) opA = C.op();
-        else if (A.op() == C.op() || C.is_real) opA = Op::NoTrans;
-        else slate_error("internal::gemm: ConjNoTrans is not supported");
-        if (opB == Op::NoTrans) opB = C.op();
-        else if (B.op() == C.op() || C.is_real) opB = Op::NoTrans;
-        else slate_error("internal::gemm: ConjNoTrans is not supported");
-    }
-    if (C.op() == Op::ConjTrans) {
-        alpha = conj(alpha);
-        beta = conj(beta);
-    }
-
     // local tiles of C and the A / B tiles they need
     std::vector<int64_t> rows, cols;
     std::vector<char> row_used(C.mt(), 0), col_used(C.nt(), 0);
@@ -133,8 +112,7 @@ void gemm(TargetType<Target::Devices>, scalar_t alpha, Matrix<scalar_t>& A, Matr
     C.tileGetForWriting(C_set, device, LayoutConvert(layout), q);
 
     const int64_t k = A.tileNb(0);
-    DescBatch batch;
-    batch.descs.reserve(C_set.size());
+    batch.descs.reserve(batch.descs.size() + C_set.size());
     const bool swap_ab = (C.op() != Op::NoTrans);
     for (size_t jb = 0; jb < cols.size(); jb += SuperBlock)
         for (size_t ib = 0; ib < rows.size(); ib += SuperBlock)
@@ -152,8 +130,62 @@ void gemm(TargetType<Target::Devices>, scalar_t alpha, Matrix<scalar_t>& A, Matr
                         batch.add(Bj.data(), Bj.stride(), Ai.data(), Ai.stride(), Cij.data(),
                                   Cij.stride(), C.tileNb(j), C.tileMb(i), k, TE_TILE_GENERAL);
                 }
+}
+}  // namespace
+
+//------------------------------------------------------------------------------
+template <typename scalar_t>
+void gemm(TargetType<Target::Devices>, scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B,
+          scalar_t beta, Matrix<scalar_t>& C, Layout layout, int priority, int64_t queue_index)
+{
+    slate_assert(layout == Layout::ColMajor);
+    slate_assert(C.mt() > 0 && C.nt() > 0);
+    slate_assert(A.nt() == 1 && B.mt() == 1);
+    slate_assert(A.mt() == C.mt() && B.nt() == C.nt());
+    slate_assert(C.num_devices() > 0);
+    const int q = (int)queue_index;
+
+    // src/internal/internal_gemm.cc:383-414: if op(C) is not NoTrans, compute the
+    // transposed product on the stored tiles.
+    Op opA = A.op(), opB = B.op();
+    if (C.op() != Op::NoTrans) {
+        if (opA == Op::NoTrans) opA = C.op();
+        else if (A.op() == C.op() || C.is_real) opA = Op::NoTrans;
+        else slate_error("internal::gemm: ConjNoTrans is not supported");
+        if (opB == Op::NoTrans) opB = C.op();
+        else if (B.op() == C.op() || C.is_real) opB = Op::NoTrans;
+        else slate_error("internal::gemm: ConjNoTrans is not supported");
+    }
+    if (C.op() == Op::ConjTrans) {
+        alpha = conj(alpha);
+        beta = conj(beta);
+    }
+
+    DescBatch batch;
+    append_gemm_tiles(batch, A, B, C, layout, q);
+    const bool swap_ab = (C.op() != Op::NoTrans);
     if (swap_ab) std::swap(opA, opB);
     launch_batch<scalar_t>(batch, q, opA, opB, alpha, beta);
+}
+
+//------------------------------------------------------------------------------
+/// Several block outer products C_p += alpha A_p B_p (+ beta C_p) in ONE launch: the parts may
+/// belong to different block steps k (a skewed schedule over column slabs of C, slate::gemm with
+/// host-origin C).  All parts share op(A), op(B) and the scalars; C must be NoTrans.
+template <typename scalar_t>
+void gemm_multi(TargetType<Target::Devices>, scalar_t alpha, std::vector<GemmPart<scalar_t>>& parts,
+                scalar_t beta, Layout layout, int64_t queue_index)
+{
+    if (parts.empty()) return;
+    const int q = (int)queue_index;
+    DescBatch batch;
+    for (auto& part : parts) {
+        slate_assert(part.C.op() == Op::NoTrans);
+        slate_assert(part.A.op() == parts[0].A.op() && part.B.op() == parts[0].B.op());
+        slate_assert(part.A.nt() == 1 && part.B.mt() == 1);
+        append_gemm_tiles(batch, part.A, part.B, part.C, layout, q);
+    }
+    launch_batch<scalar_t>(batch, q, parts[0].A.op(), parts[0].B.op(), alpha, beta);
 }
 
 //------------------------------------------------------------------------------
@@ -362,6 +394,8 @@ void reduce_info(int64_t* info, MPI_Comm comm)
 #define INSTANTIATE(T)                                                                          \
     template void gemm<T>(TargetType<Target::Devices>, T, Matrix<T>&, Matrix<T>&, T, Matrix<T>&, \
                           Layout, int, int64_t);                                                \
+    template void gemm_multi<T>(TargetType<Target::Devices>, T, std::vector<GemmPart<T>>&, T,  \
+                                Layout, int64_t);                                               \
     template void herk<T>(TargetType<Target::Devices>, real_type<T>, Matrix<T>&, real_type<T>,  \
                           HermitianMatrix<T>&, int, int, Layout);                               \
     template void syrk<T>(TargetType<Target::Devices>, T, Matrix<T>&, T, SymmetricMatrix<T>&,   \
