@@ -42,6 +42,7 @@ def hostlib():
     L.sb_gemm.argtypes = [C.c_int, C.c_int, dp, vp, vp, dp, vp, C.c_int, C.c_int,
                           C.POINTER(C.c_float)]
     L.sb_potrf.argtypes = [vp, C.c_int, C.c_int, C.POINTER(i64), C.POINTER(C.c_float)]
+    L.sb_rank_k.argtypes = [C.c_int, C.c_int, dp, vp, dp, vp, C.c_int, C.c_int]
     L.sb_potrf_residual.argtypes = [vp, i64, C.c_int, dp, dp]
     ip = C.POINTER(i64)
     L.sb_plan_gemm_step.argtypes = [vp, vp, vp, i64, ip, i64, ip]
@@ -232,6 +233,18 @@ def potrf(A, lookahead=1, target="D", timed=False):
     _check(hostlib().sb_potrf(A.h, lookahead, ord(target), C.byref(info),
                               C.byref(ms) if timed else None))
     return (info.value, ms.value) if timed else info.value
+
+
+def herk(alpha, A, beta, Cm, opa="N", lookahead=1, target="D"):
+    """slate::herk: C = alpha op(A) op(A)^H + beta C on the stored triangle of C."""
+    _check(hostlib().sb_rank_k(0, ord(opa), _scalar(alpha), A.h, _scalar(beta), Cm.h, lookahead,
+                               ord(target)))
+
+
+def syrk(alpha, A, beta, Cm, opa="N", lookahead=1, target="D"):
+    """slate::syrk: C = alpha op(A) op(A)^T + beta C on the stored triangle of C."""
+    _check(hostlib().sb_rank_k(1, ord(opa), _scalar(alpha), A.h, _scalar(beta), Cm.h, lookahead,
+                               ord(target)))
 
 
 def potrf_residual(A, seed, dominant=True):

@@ -20,6 +20,16 @@ void gemm(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t bet
 template <typename scalar_t>
 int64_t potrf(HermitianMatrix<scalar_t>& A, Options const& opts = Options());
 
+/// C = alpha A A^H + beta C, C Hermitian (src/herk.cc:15-160; include/slate/slate.hh:340-345).
+template <typename scalar_t>
+void herk(real_type<scalar_t> alpha, Matrix<scalar_t>& A, real_type<scalar_t> beta,
+          HermitianMatrix<scalar_t>& C, Options const& opts = Options());
+
+/// C = alpha A A^T + beta C, C symmetric (src/syrk.cc:15-163).
+template <typename scalar_t>
+void syrk(scalar_t alpha, Matrix<scalar_t>& A, scalar_t beta, SymmetricMatrix<scalar_t>& C,
+          Options const& opts = Options());
+
 // ---- simplified API -----------------------------------------------------------------------
 template <typename scalar_t>
 void multiply(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t beta,

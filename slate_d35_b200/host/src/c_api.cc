@@ -323,6 +323,26 @@ int sb_potrf(void* A, int lookahead, int target, int64_t* info, float* ms)
     });
 }
 
+/// slate::herk (kind = 0; alpha, beta real) or slate::syrk (kind = 1) on op(A)
+int sb_rank_k(int kind, int opa, const double* alpha, void* A, const double* beta, void* C,
+              int lookahead, int target)
+{
+    Handle *ha = (Handle*)A, *hc = (Handle*)C;
+    return guarded([&] {
+        Options opts = make_opts(target, lookahead);
+        if (hc->dtype == TE_C64) {
+            auto opA = view_op(as_general<zdouble>(ha), opa);
+            if (kind == 0) herk(alpha[0], opA, beta[0], as_herm<zdouble>(hc), opts);
+            else syrk(scalar_from<zdouble>(alpha), opA, scalar_from<zdouble>(beta), as_symm<zdouble>(hc), opts);
+        }
+        else {
+            auto opA = view_op(as_general<double>(ha), opa);
+            if (kind == 0) herk(alpha[0], opA, beta[0], as_herm<double>(hc), opts);
+            else syrk(alpha[0], opA, beta[0], as_symm<double>(hc), opts);
+        }
+    });
+}
+
 int sb_potrf_residual(void* A, int64_t seed, int dominant, double* resid_sumsq, double* a0_sumsq)
 {
     Handle* h = (Handle*)A;

@@ -172,6 +172,11 @@ def test_potrf_driver_vs_oracle(sl, origin, uplo, la):
     if origin == "H":
         other = (lambda x: np.triu(x, 1)) if uplo == "L" else (lambda x: np.tril(x, -1))
         assert np.array_equal(other(got), other(A0)), "the other triangle is not referenced"
+    if ol.have_ref() and la == 1:
+        # north star: against the reference's own HostTask path on the same matgen matrix
+        ref = A0.copy(order="F")
+        assert ol.ref().ref_dpotrf(ord(uplo), n, nb, ol.P(ref), n, 1) == 0
+        assert np.linalg.norm(tri(got) - tri(ref)) / np.linalg.norm(tri(ref)) <= 50 * EPS
 
 
 def test_potrf_info_not_positive_definite(sl):
@@ -266,3 +271,31 @@ def test_zpotrf_driver_vs_oracle(sl, uplo):
          else np.triu(A0, 1) + np.triu(A0, 1).conj().T) + np.diag(D)
     R = S - (F @ F.conj().T if uplo == "L" else F.conj().T @ F)
     assert np.linalg.norm(R) / (n * np.linalg.norm(S)) <= 50 * EPS
+
+
+# ------------------------------ herk / syrk drivers ------------------------------
+@pytest.mark.parametrize("kind", ["herk", "syrk"])
+@pytest.mark.parametrize("uplo", "LU")
+@pytest.mark.parametrize("dt", [np.float64, np.complex128])
+def test_herk_syrk_driver(sl, kind, uplo, dt):
+    """test/test_herk.cc / test_syrk.cc shapes scaled down: n = 520, k = 330, nb = 128 (ragged)."""
+    n, k, nb = 520, 330, 128
+    A0 = ol.matgen(1, n, k, dt, dist=2)
+    C0 = ol.matgen(2, n, n, dt, dist=2)
+    if kind == "herk":
+        C0[np.arange(n), np.arange(n)] = C0[np.arange(n), np.arange(n)].real
+    A = sl.Matrix(n, k, nb, dtype=dt).from_numpy(A0)
+    cls = sl.HermitianMatrix if kind == "herk" else sl.SymmetricMatrix
+    Cm = cls(uplo, n, nb, dtype=dt).from_numpy(C0)
+    if kind == "herk":
+        alpha, beta = -1.25, 0.5
+        sl.herk(alpha, A, beta, Cm)
+        full = alpha * A0 @ A0.conj().T + beta * C0
+    else:
+        alpha, beta = (-1.25 + 0.5j, 0.5 - 0.25j) if dt == np.complex128 else (-1.25, 0.5)
+        sl.syrk(alpha, A, beta, Cm)
+        full = alpha * A0 @ A0.T + beta * C0
+    got = Cm.to_numpy()
+    tri = np.tril if uplo == "L" else np.triu
+    kk = k * (4 if dt == np.complex128 else 1)
+    assert np.abs(tri(got) - tri(full)).max() <= 3 * np.sqrt(kk) * EPS * np.abs(full).max()
