@@ -82,6 +82,32 @@ def main():
                     print(f"potrf {p}x{q} la={la} {uplo}: info {info} err {err:.2e} backward {berr:.2e} "
                           f"{'ok' if ok else 'FAIL'}", flush=True)
                 H.free()
+    # herk and posv drivers on every grid: the tester's solve residual
+    for (p, q) in GRIDS[world]:
+        n, nb, nrhs, kk = 1400, 256, 10, 700
+        H = sl.HermitianMatrix("L", n, nb, p, q).generate(7, dominant=True)
+        B = sl.Matrix(n, nrhs, nb, p, q).generate(8)
+        info = sl.posv(H, B)
+        X = assemble(B)
+        Ak = sl.Matrix(n, kk, nb, p, q).generate(9, dist=2)
+        Ck = sl.HermitianMatrix("L", n, nb, p, q).generate(10, dist=2)
+        sl.herk(-1.0, Ak, 1.0, Ck)
+        Cgot = assemble(Ck)
+        if rank == 0:
+            A0 = ol.matgen(7, n, n)
+            A0[np.arange(n), np.arange(n)] += n
+            S = np.tril(A0) + np.tril(A0, -1).T
+            B0 = ol.matgen(8, n, nrhs)
+            resid = np.linalg.norm(B0 - S @ X, 1) / (n * np.linalg.norm(S, 1) * np.linalg.norm(X, 1))
+            Ak0, Ck0 = ol.matgen(9, n, kk, dist=2), ol.matgen(10, n, n, dist=2)
+            want = np.tril(-Ak0 @ Ak0.T + Ck0)
+            herr = np.abs(np.tril(Cgot) - want).max() / np.abs(want).max()
+            ok = info == 0 and resid <= 25 * EPS and herr <= 3 * np.sqrt(kk) * EPS
+            fails += (not ok)
+            print(f"posv  {p}x{q}: info {info} residual {resid:.2e}; herk err {herr:.2e} {'ok' if ok else 'FAIL'}", flush=True)
+        for M in (H, B, Ak, Ck):
+            M.free()
+
     # host-origin matrices in ScaLAPACK layout (the e2e path of bench.py): every rank passes its
     # own 2D block-cyclic local array, tiles are staged H2D / D2H around the broadcasts
     for (p, q) in GRIDS[world]:

@@ -43,6 +43,8 @@ def hostlib():
                           C.POINTER(C.c_float)]
     L.sb_potrf.argtypes = [vp, C.c_int, C.c_int, C.POINTER(i64), C.POINTER(C.c_float)]
     L.sb_rank_k.argtypes = [C.c_int, C.c_int, dp, vp, dp, vp, C.c_int, C.c_int]
+    L.sb_trsm.argtypes = [C.c_int, C.c_int, dp, vp, vp, C.c_int, C.c_int]
+    L.sb_potrs.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.POINTER(i64)]
     L.sb_potrf_residual.argtypes = [vp, i64, C.c_int, dp, dp]
     ip = C.POINTER(i64)
     L.sb_plan_gemm_step.argtypes = [vp, vp, vp, i64, ip, i64, ip]
@@ -245,6 +247,24 @@ def syrk(alpha, A, beta, Cm, opa="N", lookahead=1, target="D"):
     """slate::syrk: C = alpha op(A) op(A)^T + beta C on the stored triangle of C."""
     _check(hostlib().sb_rank_k(1, ord(opa), _scalar(alpha), A.h, _scalar(beta), Cm.h, lookahead,
                                ord(target)))
+
+
+def trsm(side, alpha, A, B, opa="N", lookahead=1, target="D"):
+    """slate::trsm: op(A) X = alpha B (side 'L') or X op(A) = alpha B (side 'R'); B <- X."""
+    _check(hostlib().sb_trsm(ord(side), ord(opa), _scalar(alpha), A.h, B.h, lookahead, ord(target)))
+
+
+def potrs(A, B, lookahead=1, target="D"):
+    """slate::potrs: solve A X = B with the Cholesky factor held in A; B <- X."""
+    info = i64()
+    _check(hostlib().sb_potrs(A.h, B.h, 0, lookahead, ord(target), C.byref(info)))
+
+
+def posv(A, B, lookahead=1, target="D"):
+    """slate::posv: factor A and solve A X = B; returns potrf's info."""
+    info = i64()
+    _check(hostlib().sb_potrs(A.h, B.h, 1, lookahead, ord(target), C.byref(info)))
+    return info.value
 
 
 def potrf_residual(A, seed, dominant=True):

@@ -200,12 +200,9 @@ public:
         : BaseTrapezoidMatrix<scalar_t>(orig), diag_(diag) {}
 
     Diag diag() const { return diag_; }
-    TriangularMatrix sub(int64_t i1, int64_t i2)
-    {
-        TriangularMatrix T(*this);
-        static_cast<BaseMatrix<scalar_t>&>(T) = BaseTrapezoidMatrix<scalar_t>(*this, i1, i2);
-        return T;
-    }
+    TriangularMatrix sub(int64_t i1, int64_t i2) { return TriangularMatrix(*this, i1, i2); }
+    TriangularMatrix(TriangularMatrix const& orig, int64_t i1, int64_t i2)
+        : BaseTrapezoidMatrix<scalar_t>(orig, i1, i2), diag_(orig.diag_) {}
     Matrix<scalar_t> sub(int64_t i1, int64_t i2, int64_t j1, int64_t j2)
     {
         return BaseTrapezoidMatrix<scalar_t>::sub(i1, i2, j1, j2);

@@ -30,6 +30,18 @@ template <typename scalar_t>
 void syrk(scalar_t alpha, Matrix<scalar_t>& A, scalar_t beta, SymmetricMatrix<scalar_t>& C,
           Options const& opts = Options());
 
+/// Triangular solve with a distributed triangular matrix: op(A) X = alpha B (side L) or
+/// X op(A) = alpha B (side R); src/trsm.cc, src/trsmB.cc, src/work/work_trsm.cc.
+template <typename scalar_t>
+void trsm(Side side, scalar_t alpha, TriangularMatrix<scalar_t>& A, Matrix<scalar_t>& B,
+          Options const& opts = Options());
+
+/// Solve with the Cholesky factor (src/potrs.cc:41-62) / factor and solve (src/posv.cc).
+template <typename scalar_t>
+void potrs(HermitianMatrix<scalar_t>& A, Matrix<scalar_t>& B, Options const& opts = Options());
+template <typename scalar_t>
+int64_t posv(HermitianMatrix<scalar_t>& A, Matrix<scalar_t>& B, Options const& opts = Options());
+
 // ---- simplified API -----------------------------------------------------------------------
 template <typename scalar_t>
 void multiply(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t beta,

@@ -343,6 +343,41 @@ int sb_rank_k(int kind, int opa, const double* alpha, void* A, const double* bet
     });
 }
 
+int sb_trsm(int side, int opa, const double* alpha, void* A, void* B, int lookahead, int target)
+{
+    Handle *ha = (Handle*)A, *hb = (Handle*)B;
+    return guarded([&] {
+        Options opts = make_opts(target, lookahead);
+        Side s = (side == 'L') ? Side::Left : Side::Right;
+        if (hb->dtype == TE_C64) {
+            auto opA = view_op(as_tri<zdouble>(ha), opa);
+            trsm(s, scalar_from<zdouble>(alpha), opA, as_general<zdouble>(hb), opts);
+        }
+        else {
+            auto opA = view_op(as_tri<double>(ha), opa);
+            trsm(s, alpha[0], opA, as_general<double>(hb), opts);
+        }
+    });
+}
+
+/// factor != 0: slate::posv (factor + solve, *info = potrf's info); else slate::potrs
+int sb_potrs(void* A, void* B, int factor, int lookahead, int target, int64_t* info)
+{
+    Handle *ha = (Handle*)A, *hb = (Handle*)B;
+    return guarded([&] {
+        Options opts = make_opts(target, lookahead);
+        *info = 0;
+        if (hb->dtype == TE_C64) {
+            if (factor) *info = posv(as_herm<zdouble>(ha), as_general<zdouble>(hb), opts);
+            else potrs(as_herm<zdouble>(ha), as_general<zdouble>(hb), opts);
+        }
+        else {
+            if (factor) *info = posv(as_herm<double>(ha), as_general<double>(hb), opts);
+            else potrs(as_herm<double>(ha), as_general<double>(hb), opts);
+        }
+    });
+}
+
 int sb_potrf_residual(void* A, int64_t seed, int dominant, double* resid_sumsq, double* a0_sumsq)
 {
     Handle* h = (Handle*)A;

@@ -299,3 +299,53 @@ def test_herk_syrk_driver(sl, kind, uplo, dt):
     tri = np.tril if uplo == "L" else np.triu
     kk = k * (4 if dt == np.complex128 else 1)
     assert np.abs(tri(got) - tri(full)).max() <= 3 * np.sqrt(kk) * EPS * np.abs(full).max()
+
+
+# ------------------------------ trsm / potrs / posv drivers ------------------------------
+@pytest.mark.parametrize("side", "LR")
+@pytest.mark.parametrize("uplo", "LU")
+@pytest.mark.parametrize("op", "NTC")
+@pytest.mark.parametrize("dt", [np.float64, np.complex128])
+def test_trsm_driver(sl, side, uplo, op, dt):
+    """test/test_trsm.cc scaled down: every side / uplo / op, ragged tiles, alpha != 1."""
+    nb = 96
+    na, other = 420, 330
+    m, n = (na, other) if side == "L" else (other, na)
+    A0 = ol.matgen(21, na, na, dt, dist=2)
+    A0[np.arange(na), np.arange(na)] += 2 * np.sqrt(na)
+    B0 = ol.matgen(22, m, n, dt, dist=2)
+    A = sl.TriangularMatrix(uplo, "N", na, nb, dtype=dt).from_numpy(A0)
+    B = sl.Matrix(m, n, nb, dtype=dt).from_numpy(B0)
+    alpha = 0.75 - 0.5j if dt == np.complex128 else 0.75
+    sl.trsm(side, alpha, A, B, opa=op)
+    X = B.to_numpy()
+    T = np.tril(A0) if uplo == "L" else np.triu(A0)
+    opT = {"N": T, "T": T.T, "C": T.conj().T}[op]
+    lhs = opT @ X if side == "L" else X @ opT
+    # residual form of the tester: || op(A) X - alpha B || / (||A|| ||X|| n)
+    err = np.linalg.norm(lhs - alpha * B0, 1) / (np.linalg.norm(T, 1) * np.linalg.norm(X, 1) * na)
+    assert err <= 3 * EPS, err
+
+
+@pytest.mark.parametrize("uplo", "LU")
+@pytest.mark.parametrize("dt", [np.float64, np.complex128])
+def test_posv_tester_check(sl, uplo, dt):
+    """the reference tester's own potrf / posv check (test/test_posv.cc:267-343): factor, solve
+    with nrhs = 10, || B - A X ||_1 / (n ||A||_1 ||X||_1) <= tol * eps / 2 with tol = 50."""
+    n, nb, nrhs = 1000, 128, 10
+    A0 = ol.matgen(7, n, n, dt)
+    A0[np.arange(n), np.arange(n)] += n
+    tri = np.tril if uplo == "L" else np.triu
+    strict = (lambda x: np.tril(x, -1)) if uplo == "L" else (lambda x: np.triu(x, 1))
+    S = strict(A0) + strict(A0).conj().T + np.diag(np.diag(A0).real)
+    B0 = ol.matgen(8, n, nrhs, dt)
+    A = sl.HermitianMatrix(uplo, n, nb, dtype=dt).from_numpy(A0)
+    B = sl.Matrix(n, nrhs, nb, dtype=dt).from_numpy(B0)
+    assert sl.posv(A, B) == 0
+    X = B.to_numpy()
+    resid = np.linalg.norm(B0 - S @ X, 1) / (n * np.linalg.norm(S, 1) * np.linalg.norm(X, 1))
+    assert resid <= 50 * EPS / 2, resid
+    # potrs on an already factored matrix gives the same solution
+    B2 = sl.Matrix(n, nrhs, nb, dtype=dt).from_numpy(B0)
+    sl.potrs(A, B2)
+    assert np.abs(B2.to_numpy() - X).max() <= 50 * EPS * np.abs(X).max()
