@@ -51,7 +51,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=128)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--n", type=int, default=N_GEMM, help="override m = n (debug only)")
+    ap.add_argument("--n", "--gemm-n", dest="n", type=int, default=N_GEMM, help="override m = n (debug only)")
     ap.add_argument("--no-potrf", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
@@ -73,8 +73,10 @@ class ClockSampler:
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index):
-        self.rows, self.proc, self.gpu = [], None, gpu_index
+    def __init__(self, gpu_indices):
+        # rank 0 samples every GPU of the job: one throttled GPU slows all ranks
+        self.rows, self.proc = [], None
+        self.gpu = ",".join(str(g) for g in gpu_indices)
 
     def start(self):
         try:
@@ -97,10 +99,11 @@ class ClockSampler:
                 self.proc.wait(timeout=5)
             except Exception:
                 self.proc.kill()
-        sm, mx, reasons = [], 0.0, set()
+        sm, mx, reasons, per_gpu = [], 0.0, set(), {}
         for r in self.rows:
             try:
                 sm.append(float(r[1]))
+                per_gpu.setdefault(int(r[0]), []).append(float(r[1]))
                 mx = max(mx, float(r[2]))
                 for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
                                       "sw_power_cap"), r[5:9]):
@@ -112,8 +115,12 @@ class ClockSampler:
         # under load = the upper half of the samples (idle gaps between phases are excluded)
         load = sm[len(sm) // 2:] if sm else []
         med = load[len(load) // 2] if load else None
-        return {"sm_mhz": med, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+        out = {"sm_mhz": med, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+               "samples": len(sm)}
+        if len(per_gpu) > 1:
+            # median of the upper half of each GPU's samples
+            out["sm_mhz_per_gpu"] = [sorted(v)[(len(v) // 2 + len(v)) // 2] for _, v in sorted(per_gpu.items())]
+        return out
 
 
 def reference_lib():
@@ -244,6 +251,14 @@ def main():
     st = te.te_peak_fp64(local_rank, 0, 20000, C.byref(peak))
     assert st == 0, te.te_last_error()
     peak_tf = peak.value
+    peaks_all = [peak_tf]
+    if world > 1:
+        # aggregate peak = sum over the GPUs of the job; peak_tf becomes their mean
+        t = torch.zeros(world, dtype=torch.float64, device="cuda")
+        t[rank] = peak_tf
+        dist.all_reduce(t)
+        peaks_all = [float(x) for x in t.tolist()]
+        peak_tf = sum(peaks_all) / world
 
     # ---- device-resident run: `value` -----------------------------------------------------
     A = sl.Matrix(n, k, nb, p, q).generate(1)
@@ -256,7 +271,7 @@ def main():
         Aw.free()
         Bw.free()
         Cm.generate(3)
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(list(range(world)) if world > 1 else [local_rank])
     if rank == 0:
         sampler.start()
     barrier()
@@ -457,6 +472,7 @@ def main():
                        "step": "one SUMMA block step (rank-512 update of C); steps=128 is the full gemm"},
             "frac_of_fp64_tensor_peak": value / (peak_tf * world),
             "fp64_dmma_peak_tflops_per_gpu": peak_tf,
+            "fp64_dmma_peak_each_gpu": [round(x, 2) for x in peaks_all],
             "gemm_error": gemm_error, "gemm_error_bound_3eps": 3 * 2.0 ** -52,
             "gpu_launches": int(launches),
             "clocks": clocks,

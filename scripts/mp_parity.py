@@ -143,6 +143,51 @@ def main():
             for M in (A, B, Cm):
                 M.free()
 
+    # the ScaLAPACK-convention entry points (include/slate_b200_scalapack.h) as an unmodified
+    # ScaLAPACK program calls them: pdgemm (with transposes) and pdposv on both rank orders
+    from slate_d35_b200 import scalapack as sc
+    for gi, (p, q) in enumerate(GRIDS[world]):
+        for order in "CR":
+            ctxt = 10 + 2 * gi + (order == "R")
+            sc.grid_set(ctxt, order, p, q)
+            myrow, mycol = (rank % p, rank // p) if order == "C" else (rank // q, rank % q)
+            m, n, k, nb, nrhs = 1500, 1300, 1100, 256, 10
+
+            def gather(local, ri, ci, shape):
+                full = np.zeros(shape)
+                full[np.ix_(ri, ci)] = local
+                t = torch.from_numpy(full).cuda()
+                dist.all_reduce(t)
+                return t.cpu().numpy()
+
+            A0, B0, C0 = ol.matgen(1, k, m), ol.matgen(2, k, n), ol.matgen(3, m, n)
+            Al, _, _ = sc.local_part(A0, nb, nb, myrow, mycol, p, q)
+            Bl, _, _ = sc.local_part(B0, nb, nb, myrow, mycol, p, q)
+            Cl, ri, ci = sc.local_part(C0, nb, nb, myrow, mycol, p, q)
+            sc.pgemm("T", "N", m, n, k, 3.141592653589793, Al, 1, 1, sc.descinit(k, m, nb, nb, ctxt, Al.shape[0]),
+                     Bl, 1, 1, sc.descinit(k, n, nb, nb, ctxt, Bl.shape[0]), 2.718281828459045,
+                     Cl, 1, 1, sc.descinit(m, n, nb, nb, ctxt, Cl.shape[0]))
+            got = gather(Cl, ri, ci, (m, n))
+            want = 3.141592653589793 * A0.T @ B0 + 2.718281828459045 * C0
+            gerr = np.abs(got - want).max() / np.abs(want).max()
+
+            nn = 1536
+            S = ol.matgen(7, nn, nn)
+            S = (S + S.T) / 2
+            S[np.arange(nn), np.arange(nn)] += nn
+            R0 = ol.matgen(8, nn, nrhs)
+            Sl, _, _ = sc.local_part(np.tril(S), nb, nb, myrow, mycol, p, q)
+            Rl, ri, ci = sc.local_part(R0, nb, nb, myrow, mycol, p, q)
+            info = sc.pposv("L", nn, nrhs, Sl, 1, 1, sc.descinit(nn, nn, nb, nb, ctxt, Sl.shape[0]),
+                            Rl, 1, 1, sc.descinit(nn, nrhs, nb, nb, ctxt, max(1, Rl.shape[0])))
+            X = gather(Rl, ri, ci, (nn, nrhs))
+            resid = np.linalg.norm(R0 - S @ X, 1) / (nn * np.linalg.norm(S, 1) * np.linalg.norm(X, 1))
+            if rank == 0:
+                ok = gerr <= 3 * np.sqrt(k) * EPS and info == 0 and resid <= 25 * EPS
+                fails += (not ok)
+                print(f"scalapack api {p}x{q} order {order}: pdgemm(T,N) err {gerr:.2e}, pdposv info {info} "
+                      f"residual {resid:.2e} {'ok' if ok else 'FAIL'}", flush=True)
+
     # info must be the same on every rank
     n, nb = 1200, 256
     p, q = GRIDS[world][0]

@@ -49,6 +49,20 @@ public:
         return M;
     }
 
+    /// include/slate/Matrix.hh:486-520, full argument list: mb x nb tiles, grid order as
+    /// BLACS reports it (scalapack_api/scalapack_slate.hh:58-78).
+    static Matrix fromScaLAPACK(int64_t m, int64_t n, scalar_t* A, int64_t lda, int64_t mb,
+                                int64_t nb, GridOrder order, int p, int q, MPI_Comm comm)
+    {
+        Matrix M(m, n, mb, nb, order, p, q, comm);
+        M.origin_ = Target::Host;
+        for (int64_t j = 0; j < M.nt(); ++j)
+            for (int64_t i = 0; i < M.mt(); ++i)
+                if (M.tileIsLocal(i, j))
+                    M.tileInsert(i, j, HostNum, &A[(i / p) * mb + (j / q) * nb * lda], lda);
+        return M;
+    }
+
     /// include/slate/Matrix.hh:832-847: SLATE-owned tiles on the host or born on the device.
     void insertLocalTiles(Target origin = Target::Host)
     {
@@ -112,6 +126,13 @@ protected:
         slate_assert(uplo == Uplo::Lower || uplo == Uplo::Upper);
         this->uplo_ = uplo;
     }
+    BaseTrapezoidMatrix(Uplo uplo, int64_t m, int64_t n, int64_t nb, GridOrder order, int p, int q,
+                        MPI_Comm comm)
+        : BaseMatrix<scalar_t>(m, n, nb, nb, order, p, q, comm)
+    {
+        slate_assert(uplo == Uplo::Lower || uplo == Uplo::Upper);
+        this->uplo_ = uplo;
+    }
     BaseTrapezoidMatrix(BaseMatrix<scalar_t> const& orig, int64_t i1, int64_t i2)
         : BaseMatrix<scalar_t>(orig, i1, i2, i1, i2) {}
     BaseTrapezoidMatrix(Uplo uplo, BaseMatrix<scalar_t> const& orig) : BaseMatrix<scalar_t>(orig)
@@ -127,6 +148,17 @@ protected:
                 if (this->tileIsLocal(i, j) && this->inStoredTriangle(i, j))
                     this->tileInsert(i, j, HostNum, &A[i * nb + j * nb * lda], lda);
     }
+
+    /// tiles of the stored triangle over a 2D block-cyclic local array
+    /// (BaseTrapezoidMatrix.hh fromScaLAPACK constructor)
+    void insertUserTilesScaLAPACK(scalar_t* A, int64_t lda, int64_t nb, int p, int q)
+    {
+        this->origin_ = Target::Host;
+        for (int64_t j = 0; j < this->nt(); ++j)
+            for (int64_t i = 0; i < this->mt(); ++i)
+                if (this->tileIsLocal(i, j) && this->inStoredTriangle(i, j))
+                    this->tileInsert(i, j, HostNum, &A[(i / p) * nb + (j / q) * nb * lda], lda);
+    }
 };
 
 //------------------------------------------------------------------------------
@@ -136,7 +168,17 @@ public:
     HermitianMatrix() {}
     HermitianMatrix(Uplo uplo, int64_t n, int64_t nb, int p, int q, MPI_Comm comm)
         : BaseTrapezoidMatrix<scalar_t>(uplo, n, n, nb, p, q, comm) {}
+    HermitianMatrix(Uplo uplo, int64_t n, int64_t nb, GridOrder order, int p, int q, MPI_Comm comm)
+        : BaseTrapezoidMatrix<scalar_t>(uplo, n, n, nb, order, p, q, comm) {}
 
+    /// HermitianMatrix.hh fromScaLAPACK (used by scalapack_api/*.cc)
+    static HermitianMatrix fromScaLAPACK(Uplo uplo, int64_t n, scalar_t* A, int64_t lda, int64_t nb,
+            GridOrder order, int p, int q, MPI_Comm comm)
+    {
+        HermitianMatrix M(uplo, n, nb, order, p, q, comm);
+        M.insertUserTilesScaLAPACK(A, lda, nb, p, q);
+        return M;
+    }
     static HermitianMatrix fromLAPACK(Uplo uplo, int64_t n, scalar_t* A, int64_t lda, int64_t nb,
                                       int p, int q, MPI_Comm comm)
     {
@@ -164,6 +206,16 @@ public:
     SymmetricMatrix() {}
     SymmetricMatrix(Uplo uplo, int64_t n, int64_t nb, int p, int q, MPI_Comm comm)
         : BaseTrapezoidMatrix<scalar_t>(uplo, n, n, nb, p, q, comm) {}
+    SymmetricMatrix(Uplo uplo, int64_t n, int64_t nb, GridOrder order, int p, int q, MPI_Comm comm)
+        : BaseTrapezoidMatrix<scalar_t>(uplo, n, n, nb, order, p, q, comm) {}
+    /// SymmetricMatrix.hh fromScaLAPACK (used by scalapack_api/*.cc)
+    static SymmetricMatrix fromScaLAPACK(Uplo uplo, int64_t n, scalar_t* A, int64_t lda, int64_t nb,
+            GridOrder order, int p, int q, MPI_Comm comm)
+    {
+        SymmetricMatrix M(uplo, n, nb, order, p, q, comm);
+        M.insertUserTilesScaLAPACK(A, lda, nb, p, q);
+        return M;
+    }
     static SymmetricMatrix fromLAPACK(Uplo uplo, int64_t n, scalar_t* A, int64_t lda, int64_t nb,
                                       int p, int q, MPI_Comm comm)
     {
@@ -186,7 +238,18 @@ public:
     TriangularMatrix() : diag_(Diag::NonUnit) {}
     TriangularMatrix(Uplo uplo, Diag diag, int64_t n, int64_t nb, int p, int q, MPI_Comm comm)
         : BaseTrapezoidMatrix<scalar_t>(uplo, n, n, nb, p, q, comm), diag_(diag) {}
+    TriangularMatrix(Uplo uplo, Diag diag, int64_t n, int64_t nb, GridOrder order, int p, int q,
+                     MPI_Comm comm)
+        : BaseTrapezoidMatrix<scalar_t>(uplo, n, n, nb, order, p, q, comm), diag_(diag) {}
 
+    /// TriangularMatrix.hh fromScaLAPACK (used by scalapack_api/*.cc)
+    static TriangularMatrix fromScaLAPACK(Uplo uplo, Diag diag, int64_t n, scalar_t* A, int64_t lda, int64_t nb,
+            GridOrder order, int p, int q, MPI_Comm comm)
+    {
+        TriangularMatrix M(uplo, diag, n, nb, order, p, q, comm);
+        M.insertUserTilesScaLAPACK(A, lda, nb, p, q);
+        return M;
+    }
     static TriangularMatrix fromLAPACK(Uplo uplo, Diag diag, int64_t n, scalar_t* A, int64_t lda,
                                        int64_t nb, int p, int q, MPI_Comm comm)
     {

@@ -154,6 +154,10 @@ public:
 
     // ---- optional per-launch device timing (SLATE_B200_TIMING) ----
     bool tracing() const { return tracing_; }
+
+    /// Set by a driver while it streams origin tiles between host and device (host-origin
+    /// gemm): descriptor arrays are then uploaded by kernel instead of by the copy engine.
+    void set_bulk_host_traffic(bool on) { bulk_host_traffic_ = on; }
     /// q >= 0: compute queue q; q == -1: the comm stream
     void trace_begin(int q, const char* what, int64_t count);
     void trace_end(int q);
@@ -191,6 +195,7 @@ private:
     std::vector<void*> event_pool_;
     std::recursive_mutex mu_;
     bool tracing_ = false;
+    bool bulk_host_traffic_ = false;
     struct TraceRec { void* e0; void* e1; const char* what; int64_t count; int q; double host_s; };
     std::vector<TraceRec> trace_;
     void* trace_epoch_ = nullptr;

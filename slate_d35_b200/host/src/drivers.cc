@@ -101,6 +101,13 @@ void gemm(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t bet
     // both transfers exposed (2 x 0.7 s for n = 65536 on one GPU).
     const bool staged = (C.origin() != Target::Devices) && C.num_devices() > 0;
     const int64_t nslab = staged ? std::max<int64_t>(1, std::min<int64_t>(8, C.nt())) : 1;
+    // origin tiles travelling over PCIe during the k loop: descriptors must not queue on the
+    // copy engine behind them (Engine::upload_desc)
+    struct BulkTrafficGuard {
+        explicit BulkTrafficGuard(bool on) { Engine::instance().set_bulk_host_traffic(on); }
+        ~BulkTrafficGuard() { Engine::instance().set_bulk_host_traffic(false); }
+    } bulk_guard(A.origin() != Target::Devices || B.origin() != Target::Devices
+                 || C.origin() != Target::Devices);
     auto slab_cols = [&](int64_t s, int64_t* j1, int64_t* j2) {
         *j1 = s * C.nt() / nslab;
         *j2 = (s + 1) * C.nt() / nslab - 1;

@@ -281,8 +281,16 @@ Engine::DescSlot& Engine::acquire_desc(int q, size_t bytes)
 
 void Engine::upload_desc(int q, DescSlot& s, size_t bytes)
 {
-    // by kernel, not by the copy engine: see te_upload_small
-    slate_te_call(te_upload_small(device_, compute_stream(q), s.dev, s.host, bytes));
+    // By kernel while bulk host<->device tile traffic is in flight (a descriptor copy would
+    // queue behind it on the copy engine, see te_upload_small); by the copy engine otherwise,
+    // which needs no SM slot -- on potrf's panel chain every extra kernel is one more wait for
+    // a slot among the trailing update's CTAs.
+    static const char* mode = std::getenv("SLATE_B200_DESC_UPLOAD");
+    bool by_kernel = mode ? (mode[0] == 'k') : bulk_host_traffic_;
+    if (by_kernel)
+        slate_te_call(te_upload_small(device_, compute_stream(q), s.dev, s.host, bytes));
+    else
+        slate_te_call(te_memcpy_async(s.dev, s.host, bytes, TE_COPY_H2D, compute_stream(q)));
 }
 
 void Engine::retire_desc(int q, DescSlot& s)

@@ -58,3 +58,41 @@ def test_product_never_links_the_oracle():
             if f.endswith((".py", ".cc", ".cu", ".hh", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "oracle_lib" not in src and "liboracle" not in src, f
+
+
+def scalapack_declared():
+    text = open(os.path.join(ROOT, "include", "slate_b200_scalapack.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(slate_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_scalapack_entry_points_are_exported():
+    """include/slate_b200_scalapack.h against libslate_b200.so, and the Fortran spellings
+    (pdgemm_, pdgemm, PDGEMM, ...) against libslate_b200_scalapack.so."""
+    from slate_d35_b200 import host
+    H = host.hostlib()
+    names = scalapack_declared()
+    assert len(names) >= 16
+    assert not [n for n in names if not hasattr(H, n)]
+    F = C.CDLL(os.path.join(ROOT, "slate_d35_b200", "lib", "libslate_b200_scalapack.so"))
+    for n in names:
+        if n.startswith("slate_p"):
+            base = n[len("slate_"):]
+            for spelling in (base, base + "_", base.upper()):
+                assert hasattr(F, spelling), spelling
+
+
+def test_scalapack_argument_errors_need_no_gpu():
+    import numpy as np
+    from slate_d35_b200 import scalapack as sc
+    with pytest.raises(ValueError):
+        sc.grid_set(0, "X", 1, 1)
+    with pytest.raises(ValueError):
+        sc.grid_set(0, "C", 0, 1)
+    a = np.zeros((64, 64), order="F")
+    d = sc.descinit(64, 64, 32, 32, 4242, 64)         # context nobody registered
+    with pytest.raises(sc.ScalapackError, match="no grid registered"):
+        sc.pgemm("N", "N", 64, 64, 64, 1.0, a, 1, 1, d, a, 1, 1, d, 0.0, a, 1, 1, d)
+    # 15 full blocks of 64 over 3 processes, the 40 left over follow the last full block
+    assert [sc.numroc(1000, 64, r, 3) for r in range(3)] == [360, 320, 320]
+    assert [sc.numroc(1100, 64, r, 3) for r in range(3)] == [384, 384, 332]
