@@ -43,6 +43,7 @@ def hostlib():
                           C.POINTER(C.c_float)]
     L.sb_potrf.argtypes = [vp, C.c_int, C.c_int, C.POINTER(i64), C.POINTER(C.c_float)]
     L.sb_rank_k.argtypes = [C.c_int, C.c_int, dp, vp, dp, vp, C.c_int, C.c_int]
+    L.sb_rank_2k.argtypes = [C.c_int, C.c_int, dp, vp, vp, dp, vp, C.c_int, C.c_int]
     L.sb_trsm.argtypes = [C.c_int, C.c_int, dp, vp, vp, C.c_int, C.c_int]
     L.sb_potrs.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.POINTER(i64)]
     L.sb_potrf_residual.argtypes = [vp, i64, C.c_int, dp, dp]
@@ -247,6 +248,18 @@ def syrk(alpha, A, beta, Cm, opa="N", lookahead=1, target="D"):
     """slate::syrk: C = alpha op(A) op(A)^T + beta C on the stored triangle of C."""
     _check(hostlib().sb_rank_k(1, ord(opa), _scalar(alpha), A.h, _scalar(beta), Cm.h, lookahead,
                                ord(target)))
+
+
+def her2k(alpha, A, B, beta, Cm, opa="N", lookahead=1, target="D"):
+    """slate::her2k: C = alpha op(A) op(B)^H + conj(alpha) op(B) op(A)^H + beta C."""
+    _check(hostlib().sb_rank_2k(0, ord(opa), _scalar(alpha), A.h, B.h, _scalar(beta), Cm.h, lookahead,
+                                ord(target)))
+
+
+def syr2k(alpha, A, B, beta, Cm, opa="N", lookahead=1, target="D"):
+    """slate::syr2k: C = alpha op(A) op(B)^T + alpha op(B) op(A)^T + beta C."""
+    _check(hostlib().sb_rank_2k(1, ord(opa), _scalar(alpha), A.h, B.h, _scalar(beta), Cm.h, lookahead,
+                                ord(target)))
 
 
 def trsm(side, alpha, A, B, opa="N", lookahead=1, target="D"):

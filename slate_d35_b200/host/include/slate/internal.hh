@@ -73,6 +73,39 @@ void syrk(scalar_t alpha, Matrix<scalar_t>&& A, scalar_t beta, SymmetricMatrix<s
     syrk(TargetType<Target::Devices>(), alpha, A, beta, C, priority, queue_index, layout);
 }
 
+// ---- her2k: C = alpha A B^H + conj(alpha) B A^H + beta C on the lower triangle of C -------
+// (src/internal/internal.hh:240-258, Devices body src/internal/internal_her2k.cc:408-660)
+template <typename scalar_t>
+void her2k(TargetType<Target::Devices>, scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B,
+           real_type<scalar_t> beta, HermitianMatrix<scalar_t>& C, int priority, int queue_index,
+           Layout layout);
+
+template <Target target = Target::HostTask, typename scalar_t>
+void her2k(scalar_t alpha, Matrix<scalar_t>&& A, Matrix<scalar_t>&& B, real_type<scalar_t> beta,
+           HermitianMatrix<scalar_t>&& C, int priority = 0, int queue_index = 0,
+           Layout layout = Layout::ColMajor)
+{
+    if (target != Target::Devices)
+        slate_not_implemented("internal::her2k: only Target::Devices is built (no CPU fallback)");
+    her2k(TargetType<Target::Devices>(), alpha, A, B, beta, C, priority, queue_index, layout);
+}
+
+// ---- syr2k: C = alpha A B^T + alpha B A^T + beta C on the lower triangle of C -------------
+// (src/internal/internal.hh:305-323, src/internal/internal_syr2k.cc:391-640)
+template <typename scalar_t>
+void syr2k(TargetType<Target::Devices>, scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B,
+           scalar_t beta, SymmetricMatrix<scalar_t>& C, int priority, int queue_index, Layout layout);
+
+template <Target target = Target::HostTask, typename scalar_t>
+void syr2k(scalar_t alpha, Matrix<scalar_t>&& A, Matrix<scalar_t>&& B, scalar_t beta,
+           SymmetricMatrix<scalar_t>&& C, int priority = 0, int queue_index = 0,
+           Layout layout = Layout::ColMajor)
+{
+    if (target != Target::Devices)
+        slate_not_implemented("internal::syr2k: only Target::Devices is built (no CPU fallback)");
+    syr2k(TargetType<Target::Devices>(), alpha, A, B, beta, C, priority, queue_index, layout);
+}
+
 // ---- trsm: B = alpha op(A)^-1 B or alpha B op(A)^-1, A one triangular tile ----------------
 template <typename scalar_t>
 void trsm(TargetType<Target::Devices>, Side side, scalar_t alpha, TriangularMatrix<scalar_t>& A,

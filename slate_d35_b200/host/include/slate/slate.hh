@@ -30,6 +30,16 @@ template <typename scalar_t>
 void syrk(scalar_t alpha, Matrix<scalar_t>& A, scalar_t beta, SymmetricMatrix<scalar_t>& C,
           Options const& opts = Options());
 
+/// C = alpha A B^H + conj(alpha) B A^H + beta C, C Hermitian (src/her2k.cc:25-190).
+template <typename scalar_t>
+void her2k(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, real_type<scalar_t> beta,
+           HermitianMatrix<scalar_t>& C, Options const& opts = Options());
+
+/// C = alpha A B^T + alpha B A^T + beta C, C symmetric (src/syr2k.cc).
+template <typename scalar_t>
+void syr2k(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t beta,
+           SymmetricMatrix<scalar_t>& C, Options const& opts = Options());
+
 /// Triangular solve with a distributed triangular matrix: op(A) X = alpha B (side L) or
 /// X op(A) = alpha B (side R); src/trsm.cc, src/trsmB.cc, src/work/work_trsm.cc.
 template <typename scalar_t>

@@ -343,6 +343,28 @@ int sb_rank_k(int kind, int opa, const double* alpha, void* A, const double* bet
     });
 }
 
+/// slate::her2k (kind = 0; beta real) or slate::syr2k (kind = 1) on op(A), op(B)
+int sb_rank_2k(int kind, int opa, const double* alpha, void* A, void* B, const double* beta, void* C,
+               int lookahead, int target)
+{
+    Handle *ha = (Handle*)A, *hb = (Handle*)B, *hc = (Handle*)C;
+    return guarded([&] {
+        Options opts = make_opts(target, lookahead);
+        if (hc->dtype == TE_C64) {
+            auto opA = view_op(as_general<zdouble>(ha), opa);
+            auto opB = view_op(as_general<zdouble>(hb), opa);
+            if (kind == 0) her2k(scalar_from<zdouble>(alpha), opA, opB, beta[0], as_herm<zdouble>(hc), opts);
+            else syr2k(scalar_from<zdouble>(alpha), opA, opB, scalar_from<zdouble>(beta), as_symm<zdouble>(hc), opts);
+        }
+        else {
+            auto opA = view_op(as_general<double>(ha), opa);
+            auto opB = view_op(as_general<double>(hb), opa);
+            if (kind == 0) her2k(alpha[0], opA, opB, beta[0], as_herm<double>(hc), opts);
+            else syr2k(alpha[0], opA, opB, beta[0], as_symm<double>(hc), opts);
+        }
+    });
+}
+
 int sb_trsm(int side, int opa, const double* alpha, void* A, void* B, int lookahead, int target)
 {
     Handle *ha = (Handle*)A, *hb = (Handle*)B;

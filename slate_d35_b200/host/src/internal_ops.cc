@@ -268,6 +268,104 @@ void syrk(TargetType<Target::Devices>, scalar_t alpha, Matrix<scalar_t>& A, scal
 }
 
 //------------------------------------------------------------------------------
+namespace {
+/// Shared body of her2k (conjugate = true) and syr2k: lower-logical C, A and B one block
+/// column each.  Two launches on the same queue, as the reference issues two batched gemms
+/// for the off-diagonal tiles (src/internal/internal_her2k.cc:520-600):
+///   1.  C(i,j) = alpha  op(A_i) op(B_j)^{H|T} + beta C(i,j)
+///   2.  C(i,j) = alpha' op(B_i) op(A_j)^{H|T} +      C(i,j),  alpha' = conj(alpha) | alpha
+/// Diagonal tiles take the same two products restricted to their stored triangle (the sum of
+/// the two triangles is the triangle of the sum); the second launch carries the Hermitian
+/// flag, which leaves the diagonal exactly real as blas::her2k does.
+template <typename scalar_t, typename CMatrix>
+void rank_2k_update(bool conjugate, scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B,
+                    scalar_t beta, CMatrix& C, int queue_index, Layout layout)
+{
+    slate_assert(layout == Layout::ColMajor);
+    slate_assert(C.num_devices() > 0);
+    slate_assert(A.nt() == 1 && B.nt() == 1);
+    slate_assert(A.mt() == C.mt() && B.mt() == C.mt() && C.mt() == C.nt());
+    slate_assert(A.op() == B.op());
+    slate_assert(C.uploLogical() == Uplo::Lower);
+    const int device = 0;
+    const int q = queue_index;
+
+    bool ok = true;
+    Op op_left = A.op();
+    Op op_right = conjugate ? conj_trans_of<scalar_t>(A.op(), &ok) : trans_of<scalar_t>(A.op(), &ok);
+    if (!ok) slate_error("internal::her2k/syr2k: op(A) mixes Trans and ConjTrans");
+    const bool swap_ij = (C.op() != Op::NoTrans);
+    if (swap_ij && is_complex<scalar_t>::value && (C.op() == Op::ConjTrans) != conjugate)
+        slate_error("internal::her2k/syr2k: op(C) does not match the update");
+    scalar_t alpha1 = alpha, alpha2 = conjugate ? conj(alpha) : alpha;
+    if (swap_ij && conjugate) {
+        // stored P = C(i,j)^H: P = conj(alpha) op(B_j) op(A_i)^H + alpha op(A_j) op(B_i)^H + conj(beta) P
+        alpha1 = conj(alpha);
+        alpha2 = alpha;
+        beta = conj(beta);
+    }
+
+    std::set<ij_tuple> AB_set, C_set;
+    for (int64_t j = 0; j < C.nt(); ++j)
+        for (int64_t i = j; i < C.mt(); ++i)
+            if (C.tileIsLocal(i, j)) {
+                C_set.insert({i, j});
+                AB_set.insert({i, 0});
+                AB_set.insert({j, 0});
+            }
+    if (C_set.empty()) return;
+    A.tileGetForReading(AB_set, device, LayoutConvert(layout), q);
+    B.tileGetForReading(AB_set, device, LayoutConvert(layout), q);
+    C.tileGetForWriting(C_set, device, LayoutConvert(layout), q);
+
+    const int64_t k = A.tileNb(0);
+    const int tri_flag = (C.uploPhysical() == Uplo::Lower ? TE_TILE_LOWER : TE_TILE_UPPER);
+    const int64_t nt = C.nt();
+    for (int pass = 0; pass < 2; ++pass) {
+        Matrix<scalar_t>& L = (pass == 0) ? A : B;      // left factor of this pass
+        Matrix<scalar_t>& R = (pass == 0) ? B : A;
+        const int diag_flag = tri_flag | ((pass == 1 && conjugate) ? TE_TILE_HERMITIAN : 0);
+        DescBatch batch;
+        batch.descs.reserve(C_set.size());
+        for (int64_t jb = 0; jb < nt; jb += SuperBlock)
+            for (int64_t ib = jb; ib < nt; ib += SuperBlock)
+                for (int64_t j = jb; j < std::min(nt, jb + SuperBlock); ++j)
+                    for (int64_t i = std::max(ib, j); i < std::min(nt, ib + SuperBlock); ++i) {
+                        if (!C.tileIsLocal(i, j)) continue;
+                        auto Li = L(i, 0, device), Lj = L(j, 0, device);
+                        auto Ri = R(i, 0, device), Rj = R(j, 0, device);
+                        auto Cij = C(i, j, device);
+                        const int flags = (i == j) ? diag_flag : TE_TILE_GENERAL;
+                        if (!swap_ij)      // C(i,j) += a op(L_i) op(R_j)^{H|T}
+                            batch.add(Li.data(), Li.stride(), Rj.data(), Rj.stride(), Cij.data(),
+                                      Cij.stride(), C.tileMb(i), C.tileNb(j), k, flags);
+                        else               // P(j,i) += a' op(R_j) op(L_i)^{H|T}
+                            batch.add(Rj.data(), Rj.stride(), Li.data(), Li.stride(), Cij.data(),
+                                      Cij.stride(), C.tileNb(j), C.tileMb(i), k, flags);
+                        (void)Lj; (void)Ri;
+                    }
+        launch_batch<scalar_t>(batch, q, op_left, op_right, pass == 0 ? alpha1 : alpha2,
+                               pass == 0 ? beta : scalar_t(1.0));
+    }
+}
+}  // namespace
+
+template <typename scalar_t>
+void her2k(TargetType<Target::Devices>, scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B,
+           real_type<scalar_t> beta, HermitianMatrix<scalar_t>& C, int priority, int queue_index,
+           Layout layout)
+{
+    rank_2k_update<scalar_t>(true, alpha, A, B, scalar_t(beta), C, queue_index, layout);
+}
+
+template <typename scalar_t>
+void syr2k(TargetType<Target::Devices>, scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B,
+           scalar_t beta, SymmetricMatrix<scalar_t>& C, int priority, int queue_index, Layout layout)
+{
+    rank_2k_update<scalar_t>(false, alpha, A, B, beta, C, queue_index, layout);
+}
+
+//------------------------------------------------------------------------------
 template <typename scalar_t>
 void trsm(TargetType<Target::Devices>, Side side, scalar_t alpha, TriangularMatrix<scalar_t>& A,
           Matrix<scalar_t>& B, int priority, Layout layout, int64_t queue_index)
@@ -400,6 +498,10 @@ void reduce_info(int64_t* info, MPI_Comm comm)
                           HermitianMatrix<T>&, int, int, Layout);                               \
     template void syrk<T>(TargetType<Target::Devices>, T, Matrix<T>&, T, SymmetricMatrix<T>&,   \
                           int, int, Layout);                                                    \
+    template void her2k<T>(TargetType<Target::Devices>, T, Matrix<T>&, Matrix<T>&,              \
+                           real_type<T>, HermitianMatrix<T>&, int, int, Layout);                \
+    template void syr2k<T>(TargetType<Target::Devices>, T, Matrix<T>&, Matrix<T>&, T,           \
+                           SymmetricMatrix<T>&, int, int, Layout);                              \
     template void trsm<T>(TargetType<Target::Devices>, Side, T, TriangularMatrix<T>&,           \
                           Matrix<T>&, int, Layout, int64_t);                                    \
     template int64_t potrf<T>(TargetType<Target::Devices>, HermitianMatrix<T>&, int, int64_t,   \

@@ -301,6 +301,46 @@ def test_herk_syrk_driver(sl, kind, uplo, dt):
     assert np.abs(tri(got) - tri(full)).max() <= 3 * np.sqrt(kk) * EPS * np.abs(full).max()
 
 
+# ------------------------------ her2k / syr2k ------------------------------
+@pytest.mark.parametrize("kind", ["her2k", "syr2k"])
+@pytest.mark.parametrize("uplo", "LU")
+@pytest.mark.parametrize("opa", "NC")
+@pytest.mark.parametrize("dt", [np.float64, np.complex128])
+def test_her2k_syr2k_driver(sl, kind, uplo, opa, dt):
+    """test/test_her2k.cc / test_syr2k.cc scaled down (ragged tiles, complex alpha, both
+    triangles, op(A) = A or its (conjugate) transpose); the diagonal of a Hermitian C comes
+    back exactly real."""
+    n, k, nb = 520, 330, 128
+    if kind == "syr2k" and opa == "C":
+        opa = "T"
+    ash = (n, k) if opa == "N" else (k, n)
+    A0 = ol.matgen(1, *ash, dt, dist=2)
+    B0 = ol.matgen(5, *ash, dt, dist=2)
+    C0 = ol.matgen(2, n, n, dt, dist=2)
+    if kind == "her2k":
+        C0[np.arange(n), np.arange(n)] = C0[np.arange(n), np.arange(n)].real
+    A = sl.Matrix(*ash, nb, dtype=dt).from_numpy(A0)
+    B = sl.Matrix(*ash, nb, dtype=dt).from_numpy(B0)
+    cls = sl.HermitianMatrix if kind == "her2k" else sl.SymmetricMatrix
+    Cm = cls(uplo, n, nb, dtype=dt).from_numpy(C0)
+    Aop, Bop = opn(A0, opa), opn(B0, opa)
+    alpha = (-1.25 + 0.5j) if dt == np.complex128 else -1.25
+    if kind == "her2k":
+        beta = 0.5
+        sl.her2k(alpha, A, B, beta, Cm, opa=opa)
+        full = alpha * Aop @ Bop.conj().T + np.conj(alpha) * Bop @ Aop.conj().T + beta * C0
+    else:
+        beta = (0.5 - 0.25j) if dt == np.complex128 else 0.5
+        sl.syr2k(alpha, A, B, beta, Cm, opa=opa)
+        full = alpha * Aop @ Bop.T + alpha * Bop @ Aop.T + beta * C0
+    got = Cm.to_numpy()
+    tri = np.tril if uplo == "L" else np.triu
+    kk = 2 * k * (4 if dt == np.complex128 else 1)
+    assert np.abs(tri(got) - tri(full)).max() <= 3 * np.sqrt(kk) * EPS * np.abs(full).max()
+    if kind == "her2k" and dt == np.complex128:
+        assert not np.diag(got).imag.any()
+
+
 # ------------------------------ trsm / potrs / posv drivers (SURVEY 8f, item 1) ------------------------------
 @pytest.mark.parametrize("side", "LR")
 @pytest.mark.parametrize("uplo", "LU")
