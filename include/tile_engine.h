@@ -285,11 +285,16 @@ int te_comm_allreduce_f64(te_comm* comm, double* buf_dev, size_t count, int op, 
  * (src/cuda/device_geadd.cu); te_tile_sumsq adds sum |a_ij|^2 over mask
  * (0 full, 1 lower, 2 upper, 3 strictly lower) to *accum_dev;
  * te_tile_keep_triangle zeroes the other strict triangle (device_tzset.cu).
+ * te_tile_scale is A = beta A with *beta of the matrix's type, zeros stored
+ * when beta == 0 (src/cuda/device_gescale.cu / device_geset.cu, as
+ * internal_gemmA.cc:312-320 uses them).
  * ---------------------------------------------------------------------- */
 int te_matgen_tile(int device, void* stream, int dtype, int dist, int64_t seed, int m, int n,
                    int64_t ioff, int64_t joff, void* A, int64_t lda, double diag_add);
 int te_tile_add(int device, void* stream, int dtype, int m, int n, double alpha, const void* A,
                 int64_t lda, double beta, void* B, int64_t ldb);
+int te_tile_scale(int device, void* stream, int dtype, int m, int n, const void* beta, void* A,
+                  int64_t lda);
 int te_tile_sumsq(int device, void* stream, int dtype, int mask, int m, int n, const void* A,
                   int64_t lda, double* accum_dev);
 int te_tile_keep_triangle(int device, void* stream, int dtype, int uplo, int m, int n, void* A,

@@ -143,6 +143,28 @@ def main():
             for M in (A, B, Cm):
                 M.free()
 
+    # gemmA (A stationary, B broadcast, partial C tiles reduced over NCCL): two block columns
+    # of B, transposed A, beta != 1; and the one-block-column case slate::gemm picks by itself
+    for (p, q) in GRIDS[world]:
+        m, k, nb = 1500, 1100, 256
+        for (n, opa, method) in ((400, "N", "A"), (400, "T", "A"), (10, "N", "auto")):
+            alpha, beta = 3.141592653589793, 2.718281828459045
+            ash = (m, k) if opa == "N" else (k, m)
+            A = sl.Matrix(*ash, nb, p, q).generate(1)
+            B = sl.Matrix(k, n, nb, p, q).generate(2)
+            Cm = sl.Matrix(m, n, nb, p, q).generate(3)
+            sl.gemm(alpha, A, B, beta, Cm, opa=opa, method=method)
+            got = assemble(Cm)
+            if rank == 0:
+                A0, B0, C0 = ol.matgen(1, *ash), ol.matgen(2, k, n), ol.matgen(3, m, n)
+                want = alpha * (A0 if opa == "N" else A0.T) @ B0 + beta * C0
+                err = np.abs(got - want).max() / np.abs(want).max()
+                ok = err <= 3 * np.sqrt(k) * EPS
+                fails += (not ok)
+                print(f"gemmA {p}x{q} n={n} op(A)={opa} method={method}: err {err:.2e} {'ok' if ok else 'FAIL'}", flush=True)
+            for M in (A, B, Cm):
+                M.free()
+
     # the ScaLAPACK-convention entry points (include/slate_b200_scalapack.h) as an unmodified
     # ScaLAPACK program calls them: pdgemm (with transposes) and pdposv on both rank orders
     from slate_d35_b200 import scalapack as sc

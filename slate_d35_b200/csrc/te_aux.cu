@@ -64,6 +64,28 @@ __global__ void tile_add_kernel(int m, int n, double alpha, const double* A, int
     B[i + j * ldb] = alpha * A[i + j * lda] + beta * B[i + j * ldb];
 }
 
+// A = beta A, beta = (br, bi); esz = doubles per element.  beta == 0 stores zeros whatever A
+// held (NaN and Inf included), as a BLAS beta = 0 does.
+__global__ void tile_scale_kernel(int m, int n, int esz, double br, double bi, double* A, int64_t lda)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= m || j >= n) return;
+    double* a = A + (int64_t)esz * (i + j * lda);
+    if (br == 0.0 && bi == 0.0) {
+        a[0] = 0.0;
+        if (esz == 2) a[1] = 0.0;
+    }
+    else if (esz == 1) {
+        a[0] = br * a[0];
+    }
+    else {
+        const double re = a[0], im = a[1];
+        a[0] = br * re - bi * im;
+        a[1] = br * im + bi * re;
+    }
+}
+
 // *accum += sum |a_ij|^2 over the masked part (mask 0 full, 1 lower incl. diag, 2 upper incl.
 // diag, 3 strictly lower).  esz = doubles per element.
 __global__ void tile_sumsq_kernel(int m, int n, int esz, int mask, const double* A, int64_t lda,
@@ -132,6 +154,22 @@ extern "C" int te_tile_add(int device, void* stream, int dtype, int m, int n, do
     dim3 grid((m * esz + 127) / 128, n);
     te::tile_add_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(
         m * esz, n, alpha, (const double*)A, lda * esz, beta, (double*)B, ldb * esz);
+    te::count_launch();
+    TE_CUDA_CHECK(cudaGetLastError());
+    return TE_OK;
+}
+
+extern "C" int te_tile_scale(int device, void* stream, int dtype, int m, int n, const void* beta,
+                             void* A, int64_t lda)
+{
+    if (!A || !beta || m < 0 || n < 0 || lda < m) return TE_ERR_ARG;
+    if (m == 0 || n == 0) return TE_OK;
+    int st = te::set_device(device);
+    if (st != TE_OK) return st;
+    const double* b = (const double*)beta;
+    dim3 grid((m + 127) / 128, n);
+    te::tile_scale_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(
+        m, n, (dtype == TE_C64) ? 2 : 1, b[0], (dtype == TE_C64) ? b[1] : 0.0, (double*)A, lda);
     te::count_launch();
     TE_CUDA_CHECK(cudaGetLastError());
     return TE_OK;

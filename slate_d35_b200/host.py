@@ -40,7 +40,7 @@ def hostlib():
     L.sb_matrix_sumsq.argtypes = [vp, dp]
     L.sb_pool_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(i64)]
     L.sb_gemm.argtypes = [C.c_int, C.c_int, dp, vp, vp, dp, vp, C.c_int, C.c_int,
-                          C.POINTER(C.c_float)]
+                          C.POINTER(C.c_float), C.c_int]
     L.sb_potrf.argtypes = [vp, C.c_int, C.c_int, C.POINTER(i64), C.POINTER(C.c_float)]
     L.sb_rank_k.argtypes = [C.c_int, C.c_int, dp, vp, dp, vp, C.c_int, C.c_int]
     L.sb_rank_2k.argtypes = [C.c_int, C.c_int, dp, vp, vp, dp, vp, C.c_int, C.c_int]
@@ -50,6 +50,7 @@ def hostlib():
     ip = C.POINTER(i64)
     L.sb_plan_gemm_step.argtypes = [vp, vp, vp, i64, ip, i64, ip]
     L.sb_plan_potrf_step.argtypes = [vp, i64, ip, i64, ip]
+    L.sb_plan_gemmA_step.argtypes = [vp, vp, vp, i64, ip, i64, ip]
     L.sb_tile_rank.argtypes = [vp, i64, i64]
     L.sb_internal_gemm.argtypes = [C.c_int, C.c_int, C.c_int, dp, vp, vp, dp, vp, C.c_int, C.c_int]
     L.sb_internal_herk.argtypes = [C.c_int, C.c_int, C.c_double, vp, C.c_double, vp, C.c_int]
@@ -222,11 +223,14 @@ class TriangularMatrix(_Base):
         return cls(uplo, diag, a.shape[0], nb, p, q, a.dtype, origin="H", host_array=a)
 
 
-def gemm(alpha, A, B, beta, Cm, opa="N", opb="N", lookahead=1, target="D", timed=False):
-    """slate::gemm: C = alpha op(A) op(B) + beta C.  Returns device milliseconds if timed."""
+def gemm(alpha, A, B, beta, Cm, opa="N", opb="N", lookahead=1, target="D", timed=False,
+         method="auto"):
+    """slate::gemm: C = alpha op(A) op(B) + beta C.  Returns device milliseconds if timed.
+    method: "auto" (gemmA when B has one block column, else gemmC), "A" or "C"."""
     ms = C.c_float()
     _check(hostlib().sb_gemm(ord(opa), ord(opb), _scalar(alpha), A.h, B.h, _scalar(beta), Cm.h,
-                             lookahead, ord(target), C.byref(ms) if timed else None))
+                             lookahead, ord(target), C.byref(ms) if timed else None,
+                             {"auto": 0, "A": 1, "C": 2}[method]))
     return ms.value if timed else None
 
 
@@ -303,6 +307,16 @@ def plan_gemm_step(A, B, Cm, k):
     buf = (i64 * cap)()
     used = i64()
     _check(hostlib().sb_plan_gemm_step(A.h, B.h, Cm.h, k, buf, cap, C.byref(used)))
+    return _unflatten(buf, used.value)
+
+
+def plan_gemmA_step(A, B, Cm, k):
+    """column k of slate::gemmA: [(0, i, j, root, dests)] for B's broadcast, then
+    [(2, i, j, root, sources)] for the reduction of C(:, k)"""
+    cap = 64 + 2 * (A.m // A.nb + A.n // A.nb + 8) * (A.p * A.q + 6)
+    buf = (i64 * cap)()
+    used = i64()
+    _check(hostlib().sb_plan_gemmA_step(A.h, B.h, Cm.h, k, buf, cap, C.byref(used)))
     return _unflatten(buf, used.value)
 
 

@@ -34,6 +34,10 @@ public:
         std::vector<std::tuple<int64_t, int64_t, std::list<BaseMatrix<scalar_t>>>>;
     using BcastListTag =
         std::vector<std::tuple<int64_t, int64_t, std::list<BaseMatrix<scalar_t>>, int64_t>>;
+    /// include/slate/BaseMatrix.hh:52-56: tile (i, j), destination view, views whose owners
+    /// hold partial sums
+    using ReduceList =
+        std::vector<std::tuple<int64_t, int64_t, BaseMatrix<scalar_t>, std::list<BaseMatrix<scalar_t>>>>;
     static constexpr bool is_complex = slate::is_complex<scalar_t>::value;
     static constexpr bool is_real = !is_complex;
 
@@ -409,6 +413,37 @@ public:
         return plan;
     }
 
+    /// One tile reduction of a plan: the partial sums of tile (i, j) held by `sources` are
+    /// added into the instance on `root`.
+    struct ReduceOp { int64_t i, j; int root; std::vector<int> sources; };
+
+    /// The host-side half of listReduce (BaseMatrix.hh:2219-2255): root = owner of the
+    /// destination view's first tile, sources = owners of the listed views, root excluded.
+    /// Entries without a remote source are dropped.
+    std::vector<ReduceOp> reducePlan(ReduceList const& reduce_list) const
+    {
+        std::vector<ReduceOp> plan;
+        for (auto const& e : reduce_list) {
+            ReduceOp op;
+            op.i = std::get<0>(e);
+            op.j = std::get<1>(e);
+            op.root = std::get<2>(e).tileRank(0, 0);
+            std::set<int> from;
+            for (auto const& S : std::get<3>(e)) S.getRanks(&from);
+            from.erase(op.root);
+            op.sources.assign(from.begin(), from.end());
+            if (!op.sources.empty()) plan.push_back(std::move(op));
+        }
+        return plan;
+    }
+
+    /// BaseMatrix.hh:2219-2255, device-resident: every source sends its partial tile to the
+    /// root over NCCL (one group for the whole list) and drops it; the root receives into
+    /// pool blocks and adds them to its tile on the comm stream.  The reference reduces on
+    /// the host over an MPI hypercube; with NVSwitch every pair has full bandwidth and the
+    /// direct pattern needs one hop.
+    void listReduce(ReduceList& reduce_list, Layout layout = Layout::ColMajor, int tag = 0);
+
     /// ranks owning at least one tile of this view (BaseMatrix.hh:3702-3756)
     void getRanks(std::set<int>* bcast_set) const
     {
@@ -601,6 +636,77 @@ void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
         eng.mark_comm();
         device_copies_pending_ = false;
     }
+}
+
+//------------------------------------------------------------------------------
+template <typename scalar_t>
+void BaseMatrix<scalar_t>::listReduce(ReduceList& reduce_list, Layout layout, int tag)
+{
+    Engine& eng = Engine::instance();
+    Comm* comm = storage_->comm_;
+    if (comm->size == 1) return;
+    const int me = comm->rank;
+    slate_assert(comm->nccl != nullptr);
+    void* stream = eng.comm_stream();
+    const int dtype = is_complex ? TE_C64 : TE_F64;
+
+    struct Incoming { ij_tuple gij; std::vector<void*> parts; };
+    std::vector<Incoming> incoming;
+    std::vector<ij_tuple> sent;
+    bool any = false;
+    for (auto const& op : reducePlan(reduce_list)) {
+        const ij_tuple gij = globalIndex(op.i, op.j);
+        if (me == op.root) {
+            // the root's own instance: on the device, about to be modified
+            tileGet(op.i, op.j, 0, true, -1);
+            auto& node = storage_->at(gij);
+            eng.comm_wait_queue_seq(node.write_queue, node.write_seq);
+            Incoming in;
+            in.gij = gij;
+            if (!any) { slate_te_call(te_comm_group_start()); any = true; }
+            for (int r : op.sources) {
+                void* part = storage_->allocScratchBlock();
+                slate_te_call(te_comm_recv(comm->nccl, part, node.dev->bytes(), r, stream));
+                in.parts.push_back(part);
+            }
+            incoming.push_back(std::move(in));
+        }
+        else if (std::find(op.sources.begin(), op.sources.end(), me) != op.sources.end()) {
+            auto* node = storage_->find(gij);
+            slate_assert(node && node->dev && node->dev_state != MOSI::Invalid);
+            slate_assert(node->dev->isContiguous());
+            eng.comm_wait_queue_seq(node->write_queue, node->write_seq);
+            if (!any) { slate_te_call(te_comm_group_start()); any = true; }
+            slate_te_call(te_comm_send(comm->nccl, node->dev->data(), node->dev->bytes(), op.root,
+                                       stream));
+            sent.push_back(gij);
+        }
+    }
+    if (!any) return;
+    eng.trace_begin(-1, "reduce", (int64_t)reduce_list.size());
+    slate_te_call(te_comm_group_end());
+    for (auto& in : incoming) {
+        auto& node = storage_->at(in.gij);
+        Tile<scalar_t>* t = node.dev;
+        for (void* part : in.parts) {
+            slate_te_call(te_tile_add(eng.device(), stream, dtype, (int)t->mb(), (int)t->nb(), 1.0, part,
+                                      t->mb(), 1.0, t->data(), t->stride()));
+            storage_->freeDeferred(part);
+        }
+        // consumers order themselves behind the comm stream, as after a broadcast
+        node.dev_state = MOSI::Modified;
+        if (node.host) node.host_state = MOSI::Invalid;
+        node.write_queue = -1;
+        node.comm_seq = eng.next_comm_seq();
+    }
+    eng.trace_end(-1);
+    // a partial sum that has been sent is spent (BaseMatrix.hh:2243-2249)
+    for (auto const& gij : sent) {
+        storage_->tileErase(gij, 0);
+        storage_->tileErase(gij, HostNum);
+    }
+    storage_->flushErased();
+    eng.mark_comm();
 }
 
 }  // namespace slate

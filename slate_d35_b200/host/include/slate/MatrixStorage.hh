@@ -147,6 +147,11 @@ public:
             tiles_.erase(it);
     }
 
+    /// A pool block used as scratch by enqueued work (listReduce receive buffers): returned
+    /// with the next flushErased().
+    void* allocScratchBlock() { return memory_.alloc(0, memory_.block_size()); }
+    void freeDeferred(void* block) { pending_free_.push_back(block); }
+
     /// Hands the device blocks dropped since the last call to the engine for deferred
     /// return to the pool.
     void flushErased()

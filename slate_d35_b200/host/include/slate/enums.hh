@@ -50,6 +50,14 @@ enum class Option : char {
     MethodGemm = 63,
 };
 
+/// include/slate/method.hh:77-98
+typedef int Method;
+namespace MethodGemm {
+const Method Auto = 0;
+const Method GemmA = 1;      ///< A stationary (src/gemmA.cc)
+const Method GemmC = 2;      ///< C stationary (src/gemmC.cc)
+}  // namespace MethodGemm
+
 enum class TileKind : char { Workspace = 'w', SlateOwned = 'o', UserOwned = 'u' };
 
 // include/slate/enums.hh:138-144

@@ -43,6 +43,21 @@ template <typename scalar_t>
 void gemm_multi(TargetType<Target::Devices>, scalar_t alpha, std::vector<GemmPart<scalar_t>>& parts,
                 scalar_t beta, Layout layout, int64_t queue_index);
 
+// ---- gemmA: C(:,0) = alpha A B(:,0) + beta C(:,0), computed where the tiles of A are -------
+// (src/internal/internal.hh gemmA, Devices body src/internal/internal_gemmA.cc:224-560)
+template <typename scalar_t>
+void gemmA(TargetType<Target::Devices>, scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B,
+           scalar_t beta, Matrix<scalar_t>& C, Layout layout, int priority, int64_t queue_index);
+
+template <Target target = Target::HostTask, typename scalar_t>
+void gemmA(scalar_t alpha, Matrix<scalar_t>&& A, Matrix<scalar_t>&& B, scalar_t beta,
+           Matrix<scalar_t>&& C, Layout layout, int priority = 0, int64_t queue_index = 0)
+{
+    if (target != Target::Devices)
+        slate_not_implemented("internal::gemmA: only Target::Devices is built (no CPU fallback)");
+    gemmA(TargetType<Target::Devices>(), alpha, A, B, beta, C, layout, priority, queue_index);
+}
+
 // ---- herk: C = alpha A A^H + beta C on the lower triangle of C ---------------------------
 template <typename scalar_t>
 void herk(TargetType<Target::Devices>, real_type<scalar_t> alpha, Matrix<scalar_t>& A,

@@ -8,11 +8,23 @@
 
 namespace slate {
 
-/// C = alpha A B + beta C.  gemmC SUMMA (src/gemm.cc:66-88, src/gemmC.cc:29-191).
-/// Options: Target (only Target::Devices is built), Lookahead (default 1).
+/// C = alpha A B + beta C (src/gemm.cc:66-88): gemmA when B has a single block column,
+/// gemmC otherwise, or as Option::MethodGemm says.
+/// Options: Target (only Target::Devices is built), Lookahead (default 1), MethodGemm.
 template <typename scalar_t>
 void gemm(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t beta,
           Matrix<scalar_t>& C, Options const& opts = Options());
+
+/// SUMMA with C stationary: panels of A and B are broadcast (src/gemmC.cc:29-191).
+template <typename scalar_t>
+void gemmC(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t beta,
+           Matrix<scalar_t>& C, Options const& opts = Options());
+
+/// A stationary: B is broadcast to where A is, partial C tiles are reduced
+/// (src/gemmA.cc:32-210).  For A much larger than B and C.
+template <typename scalar_t>
+void gemmA(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t beta,
+           Matrix<scalar_t>& C, Options const& opts = Options());
 
 /// Cholesky factorisation A = L L^H (lower) or U^H U (upper), in place
 /// (src/potrf.cc:23-210, 262-281).  Returns info: 0, or i if the leading minor of order i
@@ -67,6 +79,15 @@ int64_t chol_factor(HermitianMatrix<scalar_t>& A, Options const& opts = Options(
 }
 
 // ---- the broadcast lists of one driver step (shared by the drivers and the planners) -----
+/// src/gemmA.cc:72-78 and :110-118: the broadcast of block column k of B and the reduction of
+/// block column k of C in slate::gemmA
+template <typename scalar_t>
+typename Matrix<scalar_t>::BcastListTag gemmA_bcast_list(Matrix<scalar_t>& A, Matrix<scalar_t>& B,
+                                                         int64_t k);
+template <typename scalar_t>
+typename Matrix<scalar_t>::ReduceList gemmA_reduce_list(Matrix<scalar_t>& A, Matrix<scalar_t>& C,
+                                                        int64_t k);
+
 /// src/gemmC.cc:143-157: block column k of A to the owners of each row of C (which = 0) or
 /// block row k of B to the owners of each column of C (which = 1).
 template <typename scalar_t>

@@ -288,13 +288,15 @@ int sb_pool_stats(void* handle, int64_t* available, int64_t* capacity)
 }
 
 /// C = alpha op(A) op(B) + beta C through slate::gemm; *ms = device time of the call.
+/// method: 0 = auto (MethodGemm::select_algo), 1 = gemmA, 2 = gemmC
 int sb_gemm(int opa, int opb, const double* alpha, void* A, void* B, const double* beta, void* C,
-            int lookahead, int target, float* ms)
+            int lookahead, int target, float* ms, int method)
 {
     Handle *ha = (Handle*)A, *hb = (Handle*)B, *hc = (Handle*)C;
     return guarded([&] {
         Engine& eng = Engine::instance();
         Options opts = make_opts(target, lookahead);
+        opts[Option::MethodGemm] = (int64_t)method;
         void* t0 = ms ? eng.timer_begin() : nullptr;
         if (hc->dtype == TE_C64) {
             auto opA = view_op(as_general<zdouble>(ha), opa);
@@ -423,6 +425,28 @@ int sb_plan_gemm_step(void* A, void* B, void* C, int64_t k, int64_t* out, int64_
         auto lb = gemm_bcast_list(1, a, b, c, k);
         int64_t pos = flatten_plan(a, la, 0, out, cap, 0);
         *used = flatten_plan(b, lb, 1, out, cap, pos);
+    });
+}
+
+/// Column k of slate::gemmA: records [0, i, j, root, ndest, dest...] for the broadcast of
+/// B(:, k), then [2, i, j, root, nsource, source...] for the reduction of C(:, k).
+int sb_plan_gemmA_step(void* A, void* B, void* C, int64_t k, int64_t* out, int64_t cap, int64_t* used)
+{
+    Handle *ha = (Handle*)A, *hb = (Handle*)B, *hc = (Handle*)C;
+    return guarded([&] {
+        auto& a = as_general<double>(ha);  auto& b = as_general<double>(hb);
+        auto& c = as_general<double>(hc);
+        auto lb = gemmA_bcast_list(a, b, k);
+        int64_t pos = flatten_plan(b, lb, 0, out, cap, 0);
+        auto lr = gemmA_reduce_list(a, c, k);
+        for (auto const& op : c.reducePlan(lr)) {
+            int64_t need = 5 + (int64_t)op.sources.size();
+            if (pos + need > cap) slate_error("plan buffer too small");
+            out[pos++] = 2;  out[pos++] = op.i;  out[pos++] = op.j;  out[pos++] = op.root;
+            out[pos++] = (int64_t)op.sources.size();
+            for (int r : op.sources) out[pos++] = r;
+        }
+        *used = pos;
     });
 }
 

@@ -69,8 +69,8 @@ typename Matrix<scalar_t>::BcastListTag potrf_bcast_list(int which, HermitianMat
 
 //------------------------------------------------------------------------------
 template <typename scalar_t>
-void gemm(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t beta,
-          Matrix<scalar_t>& C, Options const& opts)
+void gemmC(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t beta,
+           Matrix<scalar_t>& C, Options const& opts)
 {
     if (get_target(opts) != Target::Devices)
         slate_not_implemented("slate::gemm: this build implements Target::Devices only "
@@ -528,7 +528,7 @@ double potrf_residual_sumsq(HermitianMatrix<scalar_t>& A, int64_t seed, bool dom
                                                                  Matrix<T>&, int64_t);         \
     template typename Matrix<T>::BcastListTag potrf_bcast_list<T>(int, HermitianMatrix<T>&,    \
                                                                   int64_t);                    \
-    template void gemm<T>(T, Matrix<T>&, Matrix<T>&, T, Matrix<T>&, Options const&);           \
+    template void gemmC<T>(T, Matrix<T>&, Matrix<T>&, T, Matrix<T>&, Options const&);          \
     template int64_t potrf<T>(HermitianMatrix<T>&, Options const&);                            \
     template void generate_rand<T>(BaseMatrix<T>&, int64_t, bool, int);                        \
     template double local_sumsq<T>(BaseMatrix<T>&);                                            \

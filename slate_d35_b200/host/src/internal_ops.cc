@@ -189,6 +189,108 @@ void gemm_multi(TargetType<Target::Devices>, scalar_t alpha, std::vector<GemmPar
 }
 
 //------------------------------------------------------------------------------
+/// C(:, 0) = alpha A B(:, 0) + beta C(:, 0) with the work placed where the tiles of A are
+/// (src/internal/internal_gemmA.cc:224-560): every rank multiplies its local A(i, j) into
+/// C(i, 0) -- a workspace tile, zeroed first, when C(i, 0) lives elsewhere -- and the caller
+/// then sums the partial tiles with listReduce.  One batched launch per block column j of A
+/// (the rows of one launch write different C tiles; consecutive launches accumulate in stream
+/// order).  beta is applied up front by a scaling pass over the C tiles this rank touches
+/// (internal_gemmA.cc:286-330 does so for untouched tiles only and passes beta to the first
+/// product; one launch has one beta here, so all tiles take the same route).
+template <typename scalar_t>
+void gemmA(TargetType<Target::Devices>, scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B,
+           scalar_t beta, Matrix<scalar_t>& C, Layout layout, int priority, int64_t queue_index)
+{
+    slate_assert(layout == Layout::ColMajor);
+    slate_assert(A.mt() == C.mt() && A.nt() == B.mt());
+    slate_assert(B.nt() == 1 && C.nt() == 1);
+    slate_assert(C.num_devices() > 0);
+    Engine& eng = Engine::instance();
+    const int device = 0;
+    const int q = (int)queue_index;
+    const int dtype = te_dtype_of<scalar_t>::value;
+    const scalar_t one = 1.0, zero = 0.0;
+
+    Op opA = A.op(), opB = B.op();
+    if (C.op() != Op::NoTrans) {
+        if (opA == Op::NoTrans) opA = C.op();
+        else if (A.op() == C.op() || C.is_real) opA = Op::NoTrans;
+        else slate_error("internal::gemmA: ConjNoTrans is not supported");
+        if (opB == Op::NoTrans) opB = C.op();
+        else if (B.op() == C.op() || C.is_real) opB = Op::NoTrans;
+        else slate_error("internal::gemmA: ConjNoTrans is not supported");
+    }
+    if (C.op() == Op::ConjTrans) {
+        alpha = conj(alpha);
+        beta = conj(beta);
+    }
+
+    // rows with local work, the B tiles they need, C tiles to create / scale
+    std::set<ij_tuple> A_set, B_set, C_local_set;
+    std::vector<int64_t> new_rows, scale_rows;
+    for (int64_t i = 0; i < A.mt(); ++i) {
+        bool touched = false;
+        for (int64_t j = 0; j < A.nt(); ++j)
+            if (A.tileIsLocal(i, j)) {
+                A_set.insert({i, j});
+                B_set.insert({j, 0});
+                touched = true;
+            }
+        if (C.tileIsLocal(i, 0)) {
+            C_local_set.insert({i, 0});
+            scale_rows.push_back(i);
+        }
+        else if (touched)
+            new_rows.push_back(i);
+    }
+    if (A_set.empty() && C_local_set.empty()) return;
+
+    A.tileGetForReading(A_set, device, LayoutConvert(layout), q);
+    B.tileGetForReading(B_set, device, LayoutConvert(layout), q);
+    C.tileGetForWriting(C_local_set, device, LayoutConvert(layout), q);
+    void* stream = eng.compute_stream(q);
+    for (int64_t i : new_rows) {
+        // partial sum for a C tile owned elsewhere
+        slate_assert(!C.tileExists(i, 0, device));
+        C.tileInsertWorkspace(i, 0, device);
+        C.tileModified(i, 0, device, q);
+        auto T = C(i, 0, device);
+        slate_te_call(te_tile_scale(eng.device(), stream, dtype, (int)T.mb(), (int)T.nb(), &zero,
+                                    T.data(), T.stride()));
+    }
+    if (beta != one)
+        for (int64_t i : scale_rows) {
+            auto T = C(i, 0, device);
+            slate_te_call(te_tile_scale(eng.device(), stream, dtype, (int)T.mb(), (int)T.nb(), &beta,
+                                        T.data(), T.stride()));
+        }
+
+    const bool swap_ab = (C.op() != Op::NoTrans);
+    if (swap_ab) std::swap(opA, opB);
+    for (int64_t j = 0; j < A.nt(); ++j) {
+        DescBatch batch;
+        for (int64_t i = 0; i < A.mt(); ++i) {
+            if (!A.tileIsLocal(i, j)) continue;
+            auto Aij = A(i, j, device);
+            auto Bj = B(j, 0, device);
+            auto Ci = C(i, 0, device);
+            if (!swap_ab)
+                batch.add(Aij.data(), Aij.stride(), Bj.data(), Bj.stride(), Ci.data(), Ci.stride(),
+                          C.tileMb(i), C.tileNb(0), A.tileNb(j), TE_TILE_GENERAL);
+            else
+                batch.add(Bj.data(), Bj.stride(), Aij.data(), Aij.stride(), Ci.data(), Ci.stride(),
+                          C.tileNb(0), C.tileMb(i), A.tileNb(j), TE_TILE_GENERAL);
+        }
+        launch_batch<scalar_t>(batch, q, opA, opB, alpha, one);
+    }
+    // the C tiles are final only after the last launch: stamp them with the mark that follows
+    // it (tileGetForWriting stamped them with the first one)
+    for (int64_t i : scale_rows) C.tileModified(i, 0, device, q);
+    for (int64_t i : new_rows) C.tileModified(i, 0, device, q);
+    eng.mark_queue(q);
+}
+
+//------------------------------------------------------------------------------
 namespace {
 /// Shared body of herk (conjugate = true) and syrk: lower-logical C, A one block column.
 template <typename scalar_t, typename CMatrix>
@@ -494,6 +596,8 @@ void reduce_info(int64_t* info, MPI_Comm comm)
                           Layout, int, int64_t);                                                \
     template void gemm_multi<T>(TargetType<Target::Devices>, T, std::vector<GemmPart<T>>&, T,  \
                                 Layout, int64_t);                                               \
+    template void gemmA<T>(TargetType<Target::Devices>, T, Matrix<T>&, Matrix<T>&, T,           \
+                           Matrix<T>&, Layout, int, int64_t);                                   \
     template void herk<T>(TargetType<Target::Devices>, real_type<T>, Matrix<T>&, real_type<T>,  \
                           HermitianMatrix<T>&, int, int, Layout);                               \
     template void syrk<T>(TargetType<Target::Devices>, T, Matrix<T>&, T, SymmetricMatrix<T>&,   \

@@ -110,6 +110,50 @@ def main():
         O.oracle_dgemm(ord("N"), ord("N"), m, n, k, nb, alpha, ol.P(A0), m, ol.P(B0), k, beta, ol.P(want), m)
         assert np.array_equal(got, want), np.abs(got - want).max()   # same tile arithmetic: bit exact
 
+    # ------------------------------ gemmA (A stationary, C reduced) ------------------------------
+    # src/gemmA.cc: B(:, kc) travels to the owners of the block columns of A, every rank
+    # multiplies its local tiles of A, partial tiles of C(:, kc) are summed onto their owners.
+    n2 = 13                                        # two block columns of B and C, the last ragged
+    B2 = sl.Matrix(k, n2, nb, p, q, origin="N")
+    C2 = sl.Matrix(m, n2, nb, p, q, origin="N")
+    B20, C20 = ol.matgen(4, k, n2), ol.matgen(5, m, n2)
+    nt2 = -(-n2 // nb)
+    b2_t, c2_t = local(B2, B20, kt, nt2), local(C2, C20, mt, nt2)
+    for kc in range(nt2):
+        ops = sl.plan_gemmA_step(A, B2, C2, kc)
+        run_bcasts(ops, 0, b2_t, rank, lambda i, j: tile_shape(k, n2, nb, i, j))
+        partial = {}
+        for i in range(mt):
+            mine = [j for j in range(kt) if sl.tile_rank(A, i, j) == rank]
+            owner = sl.tile_rank(C2, i, kc) == rank
+            if owner:
+                partial[i] = beta * c2_t[(i, kc)]
+            elif mine:
+                partial[i] = np.zeros(tile_shape(m, n2, nb, i, kc), order="F")
+            for j in mine:
+                partial[i] += alpha * a_t[(i, j)] @ b2_t[(j, kc)]   # KeyError = B tile not delivered
+        for w, i, j, root, sources in ops:
+            if w != 2:
+                continue
+            assert j == kc
+            if rank == root:
+                for src in sources:
+                    buf = torch.empty(tile_shape(m, n2, nb, i, kc), dtype=torch.float64)
+                    dist.recv(buf, src)
+                    partial[i] = partial[i] + buf.numpy()
+            elif rank in sources:
+                dist.send(torch.from_numpy(np.ascontiguousarray(partial.pop(i))), root)
+        for i, t in partial.items():
+            # whatever is left must be an owned tile: a partial sum nobody collected is a bug
+            assert sl.tile_rank(C2, i, kc) == rank, (i, kc)
+            c2_t[(i, kc)] = np.asfortranarray(t)
+        for key in [t for t in b2_t if t[1] == kc and sl.tile_rank(B2, *t) != rank]:
+            del b2_t[key]
+    got = gather_full(c2_t, C2, m, n2, nb, rank, world)
+    if rank == 0:
+        want = alpha * A0 @ B20 + beta * C20
+        assert np.abs(got - want).max() <= 3 * np.sqrt(k) * EPS * np.abs(want).max()
+
     # ------------------------------ potrf ------------------------------
     n, nb = 52, 8
     H = sl.HermitianMatrix("L", n, nb, p, q, origin="N")

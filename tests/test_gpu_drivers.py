@@ -301,6 +301,44 @@ def test_herk_syrk_driver(sl, kind, uplo, dt):
     assert np.abs(tri(got) - tri(full)).max() <= 3 * np.sqrt(kk) * EPS * np.abs(full).max()
 
 
+# ------------------------------ gemmA ------------------------------
+@pytest.mark.parametrize("dt", [np.float64, np.complex128])
+@pytest.mark.parametrize("opa,opb", [("N", "N"), ("T", "N"), ("C", "N"), ("N", "T")])
+@pytest.mark.parametrize("beta", [0.0, 1.0, 2.718281828459045])
+def test_gemmA_driver(sl, dt, opa, opb, beta):
+    """slate::gemmA (src/gemmA.cc) against gemmC and numpy: several block columns of B, ragged
+    tiles, beta = 0 must not read C (it is filled with NaN)."""
+    m, n, k, nb = 700, 300, 520, 128
+    ash = (m, k) if opa == "N" else (k, m)
+    bsh = (k, n) if opb == "N" else (n, k)
+    A0, B0, C0 = ol.matgen(1, *ash, dt, dist=2), ol.matgen(2, *bsh, dt, dist=2), ol.matgen(3, m, n, dt, dist=2)
+    alpha = (1.5 - 0.5j) if dt == np.complex128 else 3.141592653589793
+    b = (beta * (1 + 0.5j)) if dt == np.complex128 else beta
+    Cstart = np.full_like(C0, np.nan) if beta == 0.0 else C0
+    A = sl.Matrix(*ash, nb, dtype=dt).from_numpy(A0)
+    B = sl.Matrix(*bsh, nb, dtype=dt).from_numpy(B0)
+    out = {}
+    for method in "AC":
+        Cm = sl.Matrix(m, n, nb, dtype=dt).from_numpy(Cstart)
+        sl.gemm(alpha, A, B, b, Cm, opa=opa, opb=opb, method=method)
+        out[method] = Cm.to_numpy()
+    want = alpha * opn(A0, opa) @ opn(B0, opb) + (b * C0 if beta != 0.0 else 0)
+    tol = 3 * np.sqrt(k) * EPS * np.abs(want).max() * (4 if dt == np.complex128 else 1)
+    assert np.abs(out["A"] - want).max() <= tol
+    assert np.abs(out["C"] - want).max() <= tol
+
+
+def test_gemm_auto_selects_gemmA_for_one_block_column(sl):
+    """method.hh:86-98: B.nt() < 2 -> gemmA.  Both routes must agree with the tester's check."""
+    m, k, nb, nrhs = 900, 640, 128, 10
+    A0, X0 = ol.matgen(1, m, k), ol.matgen(6, k, nrhs)
+    A = sl.Matrix(m, k, nb).from_numpy(A0)
+    X = sl.Matrix(k, nrhs, nb).from_numpy(X0)
+    Y = sl.Matrix(m, nrhs, nb).from_numpy(np.zeros((m, nrhs)))
+    sl.gemm(1.0, A, X, 0.0, Y)
+    assert np.abs(Y.to_numpy() - A0 @ X0).max() <= 3 * np.sqrt(k) * EPS * np.abs(A0 @ X0).max()
+
+
 # ------------------------------ her2k / syr2k (SURVEY 8f, item 3) ------------------------------
 @pytest.mark.parametrize("kind", ["her2k", "syr2k"])
 @pytest.mark.parametrize("uplo", "LU")
