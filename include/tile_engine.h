@@ -167,6 +167,13 @@ int te_gemm_inline(int device, void* stream, int dtype, int opa, int opb,
                    const void* alpha, const void* beta,
                    const te_tile_desc* desc_host, int count);
 
+/* Scheduling hint, no reference counterpart: upper bound on the number of 128x128 output
+ * blocks one CTA of te_gemm_batched works through before it exits (default 16; 0 restores
+ * the default; the TE_ITEMS_PER_CTA environment variable overrides both).  Smaller values
+ * free SMs sooner for kernels waiting on higher-priority streams.  Process-wide; takes
+ * effect at the next launch. */
+int te_gemm_set_items_per_cta(int cap);
+
 /* ------------------------------------------------------------------------
  * Cholesky of one tile, in place:  A = L L^H (lower) or U^H U (upper).
  *
