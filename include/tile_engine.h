@@ -302,6 +302,24 @@ int te_tile_add(int device, void* stream, int dtype, int m, int n, double alpha,
                 int64_t lda, double beta, void* B, int64_t ldb);
 int te_tile_scale(int device, void* stream, int dtype, int m, int n, const void* beta, void* A,
                   int64_t lda);
+
+/* Tile transposes (src/cuda/device_transpose.cu: device::transpose and its batched forms,
+ * used by tileLayoutConvert).  AT (n x m) = A^T, or A^H if conj (complex only).  AT == A
+ * transposes in place and needs m == n, ldat == lda.  The batched form takes device arrays
+ * of `batch` tile pointers (batch <= 65535); passing the same array twice means in place. */
+int te_tile_transpose(int device, void* stream, int dtype, int conj, int m, int n, const void* A,
+                      int64_t lda, void* AT, int64_t ldat);
+int te_tile_transpose_batch(int device, void* stream, int dtype, int conj, int m, int n,
+                            const void* const* A_array_dev, int64_t lda, void* const* AT_array_dev,
+                            int64_t ldat, int batch);
+
+/* Fills the triangle of a square tile that is not stored from the one that is (uplo):
+ * A(j,i) = A(i,j), or its conjugate with the diagonal made real if hermitian.  Turns the
+ * diagonal tile of a Hermitian / symmetric matrix into a plain GEMM operand for slate::hemm /
+ * symm (the reference calls a tile hemm on the host there, src/internal/internal_hemm.cc). */
+int te_tile_symmetrize(int device, void* stream, int dtype, int uplo, int hermitian, int n, void* A,
+                       int64_t lda);
+
 int te_tile_sumsq(int device, void* stream, int dtype, int mask, int m, int n, const void* A,
                   int64_t lda, double* accum_dev);
 int te_tile_keep_triangle(int device, void* stream, int dtype, int uplo, int m, int n, void* A,

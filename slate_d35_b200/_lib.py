@@ -72,6 +72,12 @@ def lib():
                               C.c_double, vp, i64]
     L.te_tile_sumsq.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, i64, vp]
     L.te_tile_keep_triangle.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, i64]
+    L.te_tile_scale.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, vp, vp, i64]
+    L.te_tile_transpose.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, i64, vp, i64]
+    L.te_tile_transpose_batch.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, i64,
+                                          vp, i64, C.c_int]
+    L.te_tile_symmetrize.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, i64]
+    L.te_gemm_set_items_per_cta.argtypes = [C.c_int]
     L.te_device_mem_info.argtypes = [C.c_int, C.POINTER(sz), C.POINTER(sz)]
     L.te_pool_create.argtypes = [C.c_int, sz, C.POINTER(vp)]
     L.te_pool_reserve.argtypes = [vp, i64]

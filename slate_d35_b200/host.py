@@ -44,6 +44,7 @@ def hostlib():
     L.sb_potrf.argtypes = [vp, C.c_int, C.c_int, C.POINTER(i64), C.POINTER(C.c_float)]
     L.sb_rank_k.argtypes = [C.c_int, C.c_int, dp, vp, dp, vp, C.c_int, C.c_int]
     L.sb_rank_2k.argtypes = [C.c_int, C.c_int, dp, vp, vp, dp, vp, C.c_int, C.c_int]
+    L.sb_hemm.argtypes = [C.c_int, dp, vp, vp, dp, vp, C.c_int, C.c_int]
     L.sb_trsm.argtypes = [C.c_int, C.c_int, dp, vp, vp, C.c_int, C.c_int]
     L.sb_potrs.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.POINTER(i64)]
     L.sb_potrf_residual.argtypes = [vp, i64, C.c_int, dp, dp]
@@ -52,6 +53,8 @@ def hostlib():
     L.sb_plan_potrf_step.argtypes = [vp, i64, ip, i64, ip]
     L.sb_plan_gemmA_step.argtypes = [vp, vp, vp, i64, ip, i64, ip]
     L.sb_tile_rank.argtypes = [vp, i64, i64]
+    L.sb_tile_layout.argtypes = [vp, i64, i64]
+    L.sb_tile_layout_convert.argtypes = [vp, i64, i64, C.c_int]
     L.sb_internal_gemm.argtypes = [C.c_int, C.c_int, C.c_int, dp, vp, vp, dp, vp, C.c_int, C.c_int]
     L.sb_internal_herk.argtypes = [C.c_int, C.c_int, C.c_double, vp, C.c_double, vp, C.c_int]
     L.sb_internal_syrk.argtypes = [C.c_int, C.c_int, dp, vp, dp, vp, C.c_int]
@@ -169,6 +172,16 @@ class _Base:
         _check(hostlib().sb_matrix_from_host(self.h, a.ctypes.data, max(self.m, 1)))
         return self
 
+    def tile_layout(self, i, j):
+        """'C' / 'R' of the device instance of tile (i, j); None if there is none"""
+        r = hostlib().sb_tile_layout(self.h, i, j)
+        return chr(r) if r else None
+
+    def tile_layout_convert(self, i, j, layout):
+        """BaseMatrix::tileLayoutConvert of the device instance (enqueued on compute queue 0)"""
+        _check(hostlib().sb_tile_layout_convert(self.h, i, j, ord(layout)))
+        return self
+
     def sumsq(self):
         out = C.c_double()
         _check(hostlib().sb_matrix_sumsq(self.h, C.byref(out)))
@@ -264,6 +277,16 @@ def syr2k(alpha, A, B, beta, Cm, opa="N", lookahead=1, target="D"):
     """slate::syr2k: C = alpha op(A) op(B)^T + alpha op(B) op(A)^T + beta C."""
     _check(hostlib().sb_rank_2k(1, ord(opa), _scalar(alpha), A.h, B.h, _scalar(beta), Cm.h, lookahead,
                                 ord(target)))
+
+
+def hemm(side, alpha, A, B, beta, Cm, lookahead=1, target="D"):
+    """slate::hemm (A a HermitianMatrix) or slate::symm (A a SymmetricMatrix):
+    C = alpha A B + beta C (side 'L') or alpha B A + beta C (side 'R')."""
+    _check(hostlib().sb_hemm(ord(side), _scalar(alpha), A.h, B.h, _scalar(beta), Cm.h, lookahead,
+                             ord(target)))
+
+
+symm = hemm
 
 
 def trsm(side, alpha, A, B, opa="N", lookahead=1, target="D"):

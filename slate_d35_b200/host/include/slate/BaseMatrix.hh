@@ -202,29 +202,70 @@ public:
     /// the set overloads which do it); device-to-host copies wait for the producing queue
     /// and are complete on return.
     void tileGetForReading(int64_t i, int64_t j, int device = HostNum,
-                           LayoutConvert = LayoutConvert::None, int queue = -1)
+                           LayoutConvert lc = LayoutConvert::None, int queue = -1)
     {
         tileGet(i, j, device, false, queue);
         if (device == HostNum) finishHostCopies();
+        else convertIfNeeded(i, j, device, lc, queue);
     }
     void tileGetForWriting(int64_t i, int64_t j, int device = HostNum,
-                           LayoutConvert = LayoutConvert::None, int queue = -1)
+                           LayoutConvert lc = LayoutConvert::None, int queue = -1)
     {
+        // a conversion is itself a launch with its own mark: do it before the tile is stamped
+        // with the mark of the launch that is being prepared
+        if (device != HostNum && needsConvert(i, j, lc)) {
+            tileGet(i, j, device, false, queue);
+            finishSet(device, queue);
+            convertIfNeeded(i, j, device, lc, queue);
+        }
         tileGet(i, j, device, true, queue);
         if (device == HostNum) finishHostCopies();
     }
     void tileGetForReading(std::set<ij_tuple>& tiles, int device,
-                           LayoutConvert = LayoutConvert::None, int queue = -1)
+                           LayoutConvert lc = LayoutConvert::None, int queue = -1)
     {
         for (auto const& ij : tiles) tileGet(std::get<0>(ij), std::get<1>(ij), device, false, queue);
         finishSet(device, queue);
+        if (device != HostNum && lc != LayoutConvert::None)
+            for (auto const& ij : tiles) convertIfNeeded(std::get<0>(ij), std::get<1>(ij), device, lc, queue);
     }
     void tileGetForWriting(std::set<ij_tuple>& tiles, int device,
-                           LayoutConvert = LayoutConvert::None, int queue = -1)
+                           LayoutConvert lc = LayoutConvert::None, int queue = -1)
     {
+        if (device != HostNum && lc != LayoutConvert::None) {
+            // conversions first (see the single-tile overload)
+            bool any = false;
+            for (auto const& ij : tiles)
+                if (needsConvert(std::get<0>(ij), std::get<1>(ij), lc)) {
+                    tileGet(std::get<0>(ij), std::get<1>(ij), device, false, queue);
+                    any = true;
+                }
+            if (any) {
+                finishSet(device, queue);
+                for (auto const& ij : tiles)
+                    convertIfNeeded(std::get<0>(ij), std::get<1>(ij), device, lc, queue);
+            }
+        }
         for (auto const& ij : tiles) tileGet(std::get<0>(ij), std::get<1>(ij), device, true, queue);
         finishSet(device, queue);
     }
+
+    /// Layout of the instance on `device` (BaseMatrix.hh tileLayout).  Host instances are
+    /// always ColMajor in this library.
+    Layout tileLayout(int64_t i, int64_t j, int device = HostNum)
+    {
+        auto& node = storage_->at(globalIndex(i, j));
+        Tile<scalar_t>* t = (device == HostNum) ? node.host : node.dev;
+        slate_assert(t != nullptr);
+        return t->layout();
+    }
+
+    /// Transposes the stored array of the device instance so that it has `layout`
+    /// (BaseMatrix.hh tileLayoutConvert; the kernels of src/cuda/device_transpose.cu become
+    /// te_tile_transpose).  Square contiguous tiles are converted in place; rectangular ones
+    /// into a fresh pool block that replaces the old one.  Enqueued on compute queue `queue`,
+    /// or on the comm stream if queue < 0, behind the last writer of the tile.
+    void tileLayoutConvert(int64_t i, int64_t j, int device, Layout layout, int queue = -1);
     /// BaseMatrix.hh:3081-3104 (fetch_C in gemmC.cc:70-74)
     void tileGetAllForWritingOnDevices(LayoutConvert = LayoutConvert::None, int queue = -1)
     {
@@ -465,6 +506,22 @@ protected:
 
     void tileGet(int64_t i, int64_t j, int device, bool modify, int queue);
     void updateOrigin(int64_t i, int64_t j);
+    /// true if tile (i, j) has a valid device instance in the other layout
+    bool needsConvert(int64_t i, int64_t j, LayoutConvert lc)
+    {
+        if (lc == LayoutConvert::None) return false;
+        auto* node = storage_->find(globalIndex(i, j));
+        return node && node->dev && node->dev_state != MOSI::Invalid
+               && node->dev->layout() != Layout(char(lc));
+    }
+    void convertIfNeeded(int64_t i, int64_t j, int device, LayoutConvert lc, int queue)
+    {
+        if (lc == LayoutConvert::None) return;
+        auto* node = storage_->find(globalIndex(i, j));
+        if (node && node->dev && node->dev_state != MOSI::Invalid
+            && node->dev->layout() != Layout(char(lc)))
+            tileLayoutConvert(i, j, device, Layout(char(lc)), queue);
+    }
     void finishHostCopies()
     {
         if (host_copies_pending_) {
@@ -506,6 +563,9 @@ void BaseMatrix<scalar_t>::tileGet(int64_t i, int64_t j, int device, bool modify
         if (!(node.host && node.host_state != MOSI::Invalid)) {
             slate_assert(node.dev && node.dev_state != MOSI::Invalid);
             if (!node.host) storage_->tileInsert(globalIndex(i, j), HostNum, TileKind::Workspace);
+            // host instances are ColMajor: bring the device array back first (comm stream)
+            if (node.dev->layout() != Layout::ColMajor)
+                tileLayoutConvert(i, j, 0, Layout::ColMajor, -1);
             // device -> host: after the launch that produced the data
             eng.comm_wait_queue_seq(node.write_queue, node.write_seq);
             Tile<scalar_t>* s = node.dev;
@@ -537,6 +597,9 @@ void BaseMatrix<scalar_t>::tileGet(int64_t i, int64_t j, int device, bool modify
         if (!node.dev) storage_->tileInsert(globalIndex(i, j), 0, TileKind::Workspace);
         Tile<scalar_t>* s = node.host;
         Tile<scalar_t>* d = node.dev;
+        // an invalid device array left in RowMajor is simply overwritten in ColMajor
+        if (d->layout() != Layout::ColMajor && d->kind() != TileKind::UserOwned)
+            d->setLayout(Layout::ColMajor, d->mb());
         slate_te_call(te_memcpy2d_async(d->data(), sizeof(scalar_t) * d->stride(), s->data(),
                                         sizeof(scalar_t) * s->stride(), sizeof(scalar_t) * s->mb(),
                                         s->nb(), TE_COPY_H2D, eng.comm_stream()));
@@ -602,6 +665,9 @@ void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
         if (me == op.root) {
             tileGet(i, j, 0, false, -1);
             auto& node = storage_->at(globalIndex(i, j));
+            // tiles travel in ColMajor (the receivers' workspace tiles are)
+            if (node.dev->layout() != Layout::ColMajor)
+                tileLayoutConvert(i, j, 0, Layout::ColMajor, -1);
             // (a host-to-device staging copy just enqueued is on the same comm stream, ahead
             //  of the sends: stream order is enough)
             eng.comm_wait_queue_seq(node.write_queue, node.write_seq);
@@ -635,6 +701,64 @@ void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
     if (any || device_copies_pending_) {
         eng.mark_comm();
         device_copies_pending_ = false;
+    }
+}
+
+//------------------------------------------------------------------------------
+template <typename scalar_t>
+void BaseMatrix<scalar_t>::tileLayoutConvert(int64_t i, int64_t j, int device, Layout layout, int queue)
+{
+    slate_assert(device != HostNum);
+    Engine& eng = Engine::instance();
+    auto& node = storage_->at(globalIndex(i, j));
+    Tile<scalar_t>* t = node.dev;
+    slate_assert(t != nullptr && node.dev_state != MOSI::Invalid);
+    if (t->layout() == layout) return;
+    const int dtype = is_complex ? TE_C64 : TE_F64;
+    // stored array now: rows x cols column-major
+    const bool col = (t->layout() == Layout::ColMajor);
+    const int64_t tm = t->op() == Op::NoTrans ? t->mb() : t->nb();     // extents of the tile proper
+    const int64_t tn = t->op() == Op::NoTrans ? t->nb() : t->mb();
+    const int64_t rows = col ? tm : tn, cols = col ? tn : tm;
+
+    // order behind the last writer / the transfer that filled the tile
+    void* stream;
+    if (queue >= 0) {
+        if (node.write_queue >= 0 && node.write_queue != queue)
+            eng.queue_wait_queue_seq(queue, node.write_queue, node.write_seq);
+        if (node.comm_seq) eng.queue_wait_comm_seq(queue, node.comm_seq);
+        stream = eng.compute_stream(queue);
+    }
+    else {
+        eng.comm_wait_queue_seq(node.write_queue, node.write_seq);
+        stream = eng.comm_stream();
+    }
+
+    if (rows == cols && t->isContiguous()) {
+        slate_te_call(te_tile_transpose(eng.device(), stream, dtype, 0, (int)rows, (int)cols, t->data(),
+                                        t->stride(), t->data(), t->stride()));
+        t->setLayout(layout, t->stride());
+    }
+    else {
+        if (t->kind() == TileKind::UserOwned)
+            slate_error("tileLayoutConvert: a rectangular or strided user-owned device tile cannot "
+                        "be converted in place");
+        scalar_t* fresh = (scalar_t*)storage_->allocScratchBlock();
+        slate_te_call(te_tile_transpose(eng.device(), stream, dtype, 0, (int)rows, (int)cols, t->data(),
+                                        t->stride(), fresh, cols));
+        storage_->freeDeferred(t->data());
+        storage_->flushErased();
+        t->setLayout(layout, cols, fresh);
+    }
+    if (queue >= 0) {
+        node.write_queue = queue;
+        node.write_seq = eng.next_queue_seq(queue);
+        eng.mark_queue(queue);
+    }
+    else {
+        node.write_queue = -1;
+        node.comm_seq = eng.next_comm_seq();
+        eng.mark_comm();
     }
 }
 

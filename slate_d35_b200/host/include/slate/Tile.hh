@@ -51,8 +51,18 @@ public:
     bool origin() const { return kind_ != TileKind::Workspace; }
     bool workspace() const { return kind_ == TileKind::Workspace; }
     Layout layout() const { return layout_; }
+    /// After a transposition of the stored array (tileLayoutConvert): RowMajor data of an
+    /// mb x nb tile is the column-major array of its transpose, nb x mb with stride >= nb.
+    /// `data` replaces the buffer when the conversion was done out of place.
+    void setLayout(Layout layout, int64_t stride, scalar_t* data = nullptr)
+    {
+        slate_assert(stride >= (layout == Layout::ColMajor ? mb_ : nb_));
+        layout_ = layout;
+        stride_ = stride;
+        if (data) data_ = data;
+    }
     size_t bytes() const { return sizeof(scalar_t) * (size_t)mb_ * (size_t)nb_; }
-    bool isContiguous() const { return stride_ == mb_; }
+    bool isContiguous() const { return stride_ == (layout_ == Layout::ColMajor ? mb_ : nb_); }
 
     /// host element access of op(tile) (include/slate/Tile.hh:593-640); host tiles only
     scalar_t operator()(int64_t i, int64_t j) const

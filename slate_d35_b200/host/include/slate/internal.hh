@@ -58,6 +58,33 @@ void gemmA(scalar_t alpha, Matrix<scalar_t>&& A, Matrix<scalar_t>&& B, scalar_t 
     gemmA(TargetType<Target::Devices>(), alpha, A, B, beta, C, layout, priority, queue_index);
 }
 
+// ---- hemm / symm: C(0,:) = alpha A B(0,:) + beta C(0,:), A one diagonal tile ----------------
+// (src/internal/internal.hh hemm/symm; the reference has no Devices body for these and runs
+// the tile product on the host, src/internal/internal_hemm.cc -- here it runs on the GPU)
+template <typename scalar_t>
+void hemm(TargetType<Target::Devices>, Side side, scalar_t alpha, HermitianMatrix<scalar_t>& A,
+          Matrix<scalar_t>& B, scalar_t beta, Matrix<scalar_t>& C, int priority, int queue_index);
+template <typename scalar_t>
+void symm(TargetType<Target::Devices>, Side side, scalar_t alpha, SymmetricMatrix<scalar_t>& A,
+          Matrix<scalar_t>& B, scalar_t beta, Matrix<scalar_t>& C, int priority, int queue_index);
+
+template <Target target = Target::HostTask, typename scalar_t>
+void hemm(Side side, scalar_t alpha, HermitianMatrix<scalar_t>&& A, Matrix<scalar_t>&& B,
+          scalar_t beta, Matrix<scalar_t>&& C, int priority = 0, int queue_index = 0)
+{
+    if (target != Target::Devices)
+        slate_not_implemented("internal::hemm: only Target::Devices is built (no CPU fallback)");
+    hemm(TargetType<Target::Devices>(), side, alpha, A, B, beta, C, priority, queue_index);
+}
+template <Target target = Target::HostTask, typename scalar_t>
+void symm(Side side, scalar_t alpha, SymmetricMatrix<scalar_t>&& A, Matrix<scalar_t>&& B,
+          scalar_t beta, Matrix<scalar_t>&& C, int priority = 0, int queue_index = 0)
+{
+    if (target != Target::Devices)
+        slate_not_implemented("internal::symm: only Target::Devices is built (no CPU fallback)");
+    symm(TargetType<Target::Devices>(), side, alpha, A, B, beta, C, priority, queue_index);
+}
+
 // ---- herk: C = alpha A A^H + beta C on the lower triangle of C ---------------------------
 template <typename scalar_t>
 void herk(TargetType<Target::Devices>, real_type<scalar_t> alpha, Matrix<scalar_t>& A,

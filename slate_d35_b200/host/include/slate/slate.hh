@@ -52,6 +52,15 @@ template <typename scalar_t>
 void syr2k(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t beta,
            SymmetricMatrix<scalar_t>& C, Options const& opts = Options());
 
+/// C = alpha A B + beta C (side L) or alpha B A + beta C (side R), A Hermitian / symmetric with
+/// one triangle stored (src/hemm.cc, src/hemmC.cc:28-420, src/symm.cc).
+template <typename scalar_t>
+void hemm(Side side, scalar_t alpha, HermitianMatrix<scalar_t>& A, Matrix<scalar_t>& B,
+          scalar_t beta, Matrix<scalar_t>& C, Options const& opts = Options());
+template <typename scalar_t>
+void symm(Side side, scalar_t alpha, SymmetricMatrix<scalar_t>& A, Matrix<scalar_t>& B,
+          scalar_t beta, Matrix<scalar_t>& C, Options const& opts = Options());
+
 /// Triangular solve with a distributed triangular matrix: op(A) X = alpha B (side L) or
 /// X op(A) = alpha B (side R); src/trsm.cc, src/trsmB.cc, src/work/work_trsm.cc.
 template <typename scalar_t>

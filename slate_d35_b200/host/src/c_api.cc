@@ -367,6 +367,27 @@ int sb_rank_2k(int kind, int opa, const double* alpha, void* A, void* B, const d
     });
 }
 
+/// slate::hemm (A Hermitian handle) or slate::symm (A symmetric handle)
+int sb_hemm(int side, const double* alpha, void* A, void* B, const double* beta, void* C,
+            int lookahead, int target)
+{
+    Handle *ha = (Handle*)A, *hb = (Handle*)B, *hc = (Handle*)C;
+    return guarded([&] {
+        Options opts = make_opts(target, lookahead);
+        const Side sd = (side == 'R') ? Side::Right : Side::Left;
+        const bool herm = (ha->kind == 1);
+        if (hc->dtype == TE_C64) {
+            auto al = scalar_from<zdouble>(alpha), be = scalar_from<zdouble>(beta);
+            if (herm) hemm(sd, al, as_herm<zdouble>(ha), as_general<zdouble>(hb), be, as_general<zdouble>(hc), opts);
+            else symm(sd, al, as_symm<zdouble>(ha), as_general<zdouble>(hb), be, as_general<zdouble>(hc), opts);
+        }
+        else {
+            if (herm) hemm(sd, alpha[0], as_herm<double>(ha), as_general<double>(hb), beta[0], as_general<double>(hc), opts);
+            else symm(sd, alpha[0], as_symm<double>(ha), as_general<double>(hb), beta[0], as_general<double>(hc), opts);
+        }
+    });
+}
+
 int sb_trsm(int side, int opa, const double* alpha, void* A, void* B, int lookahead, int target)
 {
     Handle *ha = (Handle*)A, *hb = (Handle*)B;
@@ -461,6 +482,30 @@ int sb_plan_potrf_step(void* A, int64_t k, int64_t* out, int64_t cap, int64_t* u
         auto l1 = potrf_bcast_list(1, a, k);
         int64_t pos = flatten_plan(a, l0, 0, out, cap, 0);
         *used = flatten_plan(a, l1, 1, out, cap, pos);
+    });
+}
+
+/// Layout of the device instance of tile (i, j): 'C' or 'R'; 0 if there is none.
+int sb_tile_layout(void* A, int64_t i, int64_t j)
+{
+    Handle* h = (Handle*)A;
+    int out = 0;
+    guarded([&] {
+        DISPATCH(h,
+                 out = as_base<double>(h).tileExists(i, j, 0) ? int(as_base<double>(h).tileLayout(i, j, 0)) : 0,
+                 out = as_base<zdouble>(h).tileExists(i, j, 0) ? int(as_base<zdouble>(h).tileLayout(i, j, 0)) : 0);
+    });
+    return out;
+}
+
+/// BaseMatrix::tileLayoutConvert on the device instance of tile (i, j), compute queue 0.
+int sb_tile_layout_convert(void* A, int64_t i, int64_t j, int layout)
+{
+    Handle* h = (Handle*)A;
+    return guarded([&] {
+        const Layout l = (layout == 'R') ? Layout::RowMajor : Layout::ColMajor;
+        DISPATCH(h, as_base<double>(h).tileLayoutConvert(i, j, 0, l, 0),
+                 as_base<zdouble>(h).tileLayoutConvert(i, j, 0, l, 0));
     });
 }
 

@@ -292,6 +292,105 @@ void gemmA(TargetType<Target::Devices>, scalar_t alpha, Matrix<scalar_t>& A, Mat
 
 //------------------------------------------------------------------------------
 namespace {
+/// Shared body of hemm (hermitian = true) and symm: C(0, :) = alpha A B(0, :) + beta C(0, :)
+/// with A one diagonal tile of which only the uplo triangle is stored.  The reference runs a
+/// tile hemm on the host here even for Target::Devices (src/internal/internal_hemm.cc, called
+/// from src/hemmC.cc:146-151); on this engine the tile is copied into a pool block, its other
+/// triangle filled in (te_tile_symmetrize), and the copy is an ordinary operand of the batched
+/// GEMM kernel.
+template <typename scalar_t, typename AMatrix>
+void diag_tile_mm(bool hermitian, Side side, scalar_t alpha, AMatrix& A, Matrix<scalar_t>& B,
+                  scalar_t beta, Matrix<scalar_t>& C, int queue_index)
+{
+    slate_assert(side == Side::Left);               // drivers turn Right into Left by views
+    slate_assert(A.mt() == 1 && A.nt() == 1);
+    slate_assert(B.mt() == 1 && C.mt() == 1 && B.nt() == C.nt());
+    slate_assert(C.num_devices() > 0);
+    Engine& eng = Engine::instance();
+    const int device = 0;
+    const int q = queue_index;
+    const int dtype = te_dtype_of<scalar_t>::value;
+
+    // op(A) of the filled tile: A itself if the view is untransposed, and also if the view's op
+    // matches the matrix kind (A^H = A, A^T = A); anything else would be conj(A)
+    const Op same_op = hermitian ? Op::ConjTrans : Op::Trans;
+    Op opA = Op::NoTrans;
+    if (A.op() != Op::NoTrans && A.op() != same_op && is_complex<scalar_t>::value)
+        opA = (A.op() == Op::Trans) ? Op::Trans : Op::ConjTrans;   // conj(A) = (A^H)^T = (A^T)^H
+    Op opB = B.op();
+    if (C.op() != Op::NoTrans) {
+        // stored P = op(C): P = op(B) op(A), as in internal::gemm
+        if (opA == Op::NoTrans) opA = (C.op() == same_op || C.is_real) ? Op::NoTrans : C.op();
+        else if (opA == C.op() || C.is_real) opA = Op::NoTrans;
+        else slate_error("internal::hemm/symm: ConjNoTrans is not supported");
+        if (opB == Op::NoTrans) opB = C.op();
+        else if (B.op() == C.op() || C.is_real) opB = Op::NoTrans;
+        else slate_error("internal::hemm/symm: ConjNoTrans is not supported");
+    }
+    if (C.op() == Op::ConjTrans) {
+        alpha = conj(alpha);
+        beta = conj(beta);
+    }
+
+    std::set<ij_tuple> A_set{{0, 0}}, B_set, C_set;
+    for (int64_t j = 0; j < C.nt(); ++j)
+        if (C.tileIsLocal(0, j)) {
+            C_set.insert({0, j});
+            B_set.insert({0, j});
+        }
+    if (C_set.empty()) return;
+    A.tileGetForReading(A_set, device, LayoutConvert::ColMajor, q);
+    B.tileGetForReading(B_set, device, LayoutConvert::ColMajor, q);
+    C.tileGetForWriting(C_set, device, LayoutConvert::ColMajor, q);
+
+    // full copy of the diagonal tile
+    auto A00 = A(0, 0, device);
+    const int64_t n = A00.mb();
+    slate_assert(A00.nb() == n);
+    void* stream = eng.compute_stream(q);
+    scalar_t* full = (scalar_t*)A.storage()->allocScratchBlock();
+    slate_te_call(te_memcpy2d_async(full, sizeof(scalar_t) * n, A00.data(), sizeof(scalar_t) * A00.stride(),
+                                    sizeof(scalar_t) * n, n, TE_COPY_D2D, stream));
+    slate_te_call(te_tile_symmetrize(eng.device(), stream, dtype,
+                                     A00.uploPhysical() == Uplo::Lower ? TE_UPLO_LOWER : TE_UPLO_UPPER,
+                                     hermitian ? 1 : 0, (int)n, full, n));
+
+    DescBatch batch;
+    const bool swap_ab = (C.op() != Op::NoTrans);
+    for (int64_t j = 0; j < C.nt(); ++j) {
+        if (!C.tileIsLocal(0, j)) continue;
+        auto Bj = B(0, j, device);
+        auto Cj = C(0, j, device);
+        if (!swap_ab)
+            batch.add(full, n, Bj.data(), Bj.stride(), Cj.data(), Cj.stride(), C.tileMb(0),
+                      C.tileNb(j), n, TE_TILE_GENERAL);
+        else
+            batch.add(Bj.data(), Bj.stride(), full, n, Cj.data(), Cj.stride(), C.tileNb(j),
+                      C.tileMb(0), n, TE_TILE_GENERAL);
+    }
+    if (swap_ab) std::swap(opA, opB);
+    launch_batch<scalar_t>(batch, q, opA, opB, alpha, beta);
+    A.storage()->freeDeferred(full);
+    A.storage()->flushErased();
+}
+}  // namespace
+
+template <typename scalar_t>
+void hemm(TargetType<Target::Devices>, Side side, scalar_t alpha, HermitianMatrix<scalar_t>& A,
+          Matrix<scalar_t>& B, scalar_t beta, Matrix<scalar_t>& C, int priority, int queue_index)
+{
+    diag_tile_mm<scalar_t>(true, side, alpha, A, B, beta, C, queue_index);
+}
+
+template <typename scalar_t>
+void symm(TargetType<Target::Devices>, Side side, scalar_t alpha, SymmetricMatrix<scalar_t>& A,
+          Matrix<scalar_t>& B, scalar_t beta, Matrix<scalar_t>& C, int priority, int queue_index)
+{
+    diag_tile_mm<scalar_t>(false, side, alpha, A, B, beta, C, queue_index);
+}
+
+//------------------------------------------------------------------------------
+namespace {
 /// Shared body of herk (conjugate = true) and syrk: lower-logical C, A one block column.
 template <typename scalar_t, typename CMatrix>
 void rank_k_update(bool conjugate, scalar_t alpha, Matrix<scalar_t>& A, scalar_t beta, CMatrix& C,
@@ -598,6 +697,10 @@ void reduce_info(int64_t* info, MPI_Comm comm)
                                 Layout, int64_t);                                               \
     template void gemmA<T>(TargetType<Target::Devices>, T, Matrix<T>&, Matrix<T>&, T,           \
                            Matrix<T>&, Layout, int, int64_t);                                   \
+    template void hemm<T>(TargetType<Target::Devices>, Side, T, HermitianMatrix<T>&, Matrix<T>&, \
+                          T, Matrix<T>&, int, int);                                             \
+    template void symm<T>(TargetType<Target::Devices>, Side, T, SymmetricMatrix<T>&, Matrix<T>&, \
+                          T, Matrix<T>&, int, int);                                             \
     template void herk<T>(TargetType<Target::Devices>, real_type<T>, Matrix<T>&, real_type<T>,  \
                           HermitianMatrix<T>&, int, int, Layout);                               \
     template void syrk<T>(TargetType<Target::Devices>, T, Matrix<T>&, T, SymmetricMatrix<T>&,   \

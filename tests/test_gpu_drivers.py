@@ -379,6 +379,76 @@ def test_her2k_syr2k_driver(sl, kind, uplo, opa, dt):
         assert not np.diag(got).imag.any()
 
 
+# ------------------------------ RowMajor tiles ------------------------------
+@pytest.mark.parametrize("dt", [np.float64, np.complex128])
+def test_tile_layout_convert_round_trip_and_gemm(sl, dt):
+    """tileLayoutConvert (src/cuda/device_transpose.cu behind it): square tiles in place,
+    ragged edge tiles out of place; the matrix reads back unchanged, and a gemm on RowMajor
+    tiles (converted back by the internal op, LayoutConvert::ColMajor) gives the same bits as
+    on untouched tiles."""
+    m, n, k, nb = 300, 200, 280, 128                 # last tile row / column ragged
+    A0, B0, C0 = ol.matgen(1, m, k, dt, dist=2), ol.matgen(2, k, n, dt, dist=2), ol.matgen(3, m, n, dt, dist=2)
+    A = sl.Matrix(m, k, nb, dtype=dt).from_numpy(A0)
+    mt, kt = -(-m // nb), -(-k // nb)
+    for i in range(mt):
+        for j in range(kt):
+            assert A.tile_layout(i, j) == "C"
+            A.tile_layout_convert(i, j, "R")
+            assert A.tile_layout(i, j) == "R"
+    assert np.array_equal(A.to_numpy(), A0)            # reading converts back
+    assert A.tile_layout(0, 0) == "C"
+    # twice in a row, through both layouts
+    A.tile_layout_convert(mt - 1, kt - 1, "R").tile_layout_convert(mt - 1, kt - 1, "C")
+    assert np.array_equal(A.to_numpy(), A0)
+
+    out = []
+    for rowmajor in (False, True):
+        A = sl.Matrix(m, k, nb, dtype=dt).from_numpy(A0)
+        B = sl.Matrix(k, n, nb, dtype=dt).from_numpy(B0)
+        Cm = sl.Matrix(m, n, nb, dtype=dt).from_numpy(C0)
+        if rowmajor:
+            for M, rows, cols in ((A, m, k), (B, k, n), (Cm, m, n)):
+                for i in range(-(-rows // nb)):
+                    for j in range(-(-cols // nb)):
+                        M.tile_layout_convert(i, j, "R")
+        sl.gemm(ALPHA, A, B, BETA, Cm)
+        out.append(Cm.to_numpy())
+    assert np.array_equal(out[0], out[1])
+    want = ALPHA * A0 @ B0 + BETA * C0
+    assert np.abs(out[1] - want).max() <= 12 * np.sqrt(k) * EPS * np.abs(want).max()
+
+
+# ------------------------------ hemm / symm (SURVEY 8f, item 3) ------------------------------
+@pytest.mark.parametrize("kind", ["hemm", "symm"])
+@pytest.mark.parametrize("side", "LR")
+@pytest.mark.parametrize("uplo", "LU")
+@pytest.mark.parametrize("dt", [np.float64, np.complex128])
+def test_hemm_symm_driver(sl, kind, side, uplo, dt):
+    """test/test_hemm.cc / test_symm.cc scaled down: both sides and triangles, ragged tiles,
+    complex alpha and beta; the triangle of A that is not stored holds NaN."""
+    na, other, nb = 520, 330, 128
+    m, n = (na, other) if side == "L" else (other, na)
+    A0 = ol.matgen(41, na, na, dt, dist=2)
+    if kind == "hemm":
+        S = (A0 + A0.conj().T) / 2
+    else:
+        S = (A0 + A0.T) / 2
+    tri = np.tril if uplo == "L" else np.triu
+    other_strict = (lambda x: np.triu(x, 1)) if uplo == "L" else (lambda x: np.tril(x, -1))
+    stored = tri(S).astype(dt) + other_strict(np.full((na, na), np.nan))
+    B0, C0 = ol.matgen(42, m, n, dt, dist=2), ol.matgen(43, m, n, dt, dist=2)
+    cls = sl.HermitianMatrix if kind == "hemm" else sl.SymmetricMatrix
+    A = cls(uplo, na, nb, dtype=dt).from_numpy(stored)
+    B = sl.Matrix(m, n, nb, dtype=dt).from_numpy(B0)
+    Cm = sl.Matrix(m, n, nb, dtype=dt).from_numpy(C0)
+    alpha, beta = ((1.5 - 0.5j), (0.25 + 2j)) if dt == np.complex128 else (3.141592653589793, 2.718281828459045)
+    sl.hemm(side, alpha, A, B, beta, Cm)
+    want = alpha * (S @ B0 if side == "L" else B0 @ S) + beta * C0
+    got = Cm.to_numpy()
+    kk = na * (4 if dt == np.complex128 else 1)
+    assert np.abs(got - want).max() <= 3 * np.sqrt(kk) * EPS * np.abs(want).max()
+
+
 # ------------------------------ trsm / potrs / posv drivers (SURVEY 8f, item 1) ------------------------------
 @pytest.mark.parametrize("side", "LR")
 @pytest.mark.parametrize("uplo", "LU")

@@ -373,3 +373,89 @@ def test_ztrsm_batched_vs_oracle(te, side, uplo, op, diag):
         got = host(dB, (m, n), np.complex128)
         err = np.abs(got - want).max() / np.abs(want).max()
         assert err <= 50 * EPS * np.sqrt(na), (err, side, uplo, op, diag)
+
+
+# ------------------------------ transposes, symmetric fill, scaling ------------------------------
+@pytest.mark.parametrize("dt", [np.float64, np.complex128])
+@pytest.mark.parametrize("m,n,pad", [(512, 512, 0), (384, 130, 5), (33, 97, 1), (1, 7, 0)])
+@pytest.mark.parametrize("conj", [0, 1])
+def test_tile_transpose_out_of_place(te, dt, m, n, pad, conj):
+    """src/cuda/device_transpose.cu, rectangular form: AT = A^T (A^H), bit exact, padding rows
+    of both arrays untouched."""
+    from slate_d35_b200 import check
+    A0 = ol.matgen(31, m + pad, n, dt, dist=2)
+    T0 = ol.matgen(32, n + pad, m, dt, dist=2)
+    a, t = dev(A0), dev(T0)
+    check(te.te_tile_transpose(0, stream(), DT[dt], conj, m, n, a.data_ptr(), m + pad, t.data_ptr(), n + pad))
+    got = host(t, (n + pad, m), dt)
+    want = A0[:m].conj().T if (conj and dt == np.complex128) else A0[:m].T
+    assert np.array_equal(got[:n], want)
+    assert np.array_equal(got[n:], T0[n:])
+    assert np.array_equal(host(a, (m + pad, n), dt), A0)
+
+
+@pytest.mark.parametrize("dt", [np.float64, np.complex128])
+@pytest.mark.parametrize("n,pad", [(512, 0), (200, 3), (31, 0), (65, 2)])
+def test_tile_transpose_in_place_and_batched(te, dt, n, pad):
+    """square in-place form and the batched forms (device arrays of tile pointers)."""
+    import torch
+    from slate_d35_b200 import check
+    A0 = ol.matgen(33, n + pad, n, dt, dist=2)
+    a = dev(A0)
+    check(te.te_tile_transpose(0, stream(), DT[dt], 1, n, n, a.data_ptr(), n + pad, a.data_ptr(), n + pad))
+    got = host(a, (n + pad, n), dt)
+    assert np.array_equal(got[:n], A0[:n].conj().T) and np.array_equal(got[n:], A0[n:])
+    # a mismatched in-place call is refused
+    assert te.te_tile_transpose(0, stream(), DT[dt], 0, n, n - 1, a.data_ptr(), n + pad, a.data_ptr(), n + pad) != 0
+
+    batch = 5
+    tiles = [ol.matgen(40 + b, n + pad, n, dt, dist=2) for b in range(batch)]
+    d_in = [dev(x) for x in tiles]
+    d_out = [dev(np.zeros((n, n), dtype=dt, order="F")) for _ in range(batch)]
+    p_in = torch.tensor([x.data_ptr() for x in d_in], dtype=torch.int64, device="cuda")
+    p_out = torch.tensor([x.data_ptr() for x in d_out], dtype=torch.int64, device="cuda")
+    check(te.te_tile_transpose_batch(0, stream(), DT[dt], 0, n, n, p_in.data_ptr(), n + pad, p_out.data_ptr(), n, batch))
+    for b in range(batch):
+        assert np.array_equal(host(d_out[b], (n, n), dt), tiles[b][:n].T)
+    check(te.te_tile_transpose_batch(0, stream(), DT[dt], 0, n, n, p_in.data_ptr(), n + pad, p_in.data_ptr(), n + pad, batch))
+    for b in range(batch):
+        got = host(d_in[b], (n + pad, n), dt)
+        assert np.array_equal(got[:n], tiles[b][:n].T) and np.array_equal(got[n:], tiles[b][n:])
+
+
+@pytest.mark.parametrize("dt", [np.float64, np.complex128])
+@pytest.mark.parametrize("uplo", "LU")
+@pytest.mark.parametrize("herm", [0, 1])
+@pytest.mark.parametrize("n,pad", [(512, 0), (100, 4), (33, 0)])
+def test_tile_symmetrize(te, dt, uplo, herm, n, pad):
+    from slate_d35_b200 import check
+    A0 = ol.matgen(34, n + pad, n, dt, dist=2)
+    a = dev(A0)
+    check(te.te_tile_symmetrize(0, stream(), DT[dt], ord(uplo), herm, n, a.data_ptr(), n + pad))
+    got = host(a, (n + pad, n), dt)
+    S = A0[:n]
+    strict = np.tril(S, -1) if uplo == "L" else np.triu(S, 1)
+    d = np.diag(np.diag(S))
+    if herm and dt == np.complex128:
+        want = strict + strict.conj().T + d.real
+    else:
+        want = strict + strict.T + d
+    assert np.array_equal(got[:n], want) and np.array_equal(got[n:], A0[n:])
+
+
+@pytest.mark.parametrize("dt", [np.float64, np.complex128])
+@pytest.mark.parametrize("beta", [0.0, 1.0, -0.75])
+def test_tile_scale(te, dt, beta):
+    """device_gescale / geset: A = beta A; beta = 0 stores zeros over NaN."""
+    from slate_d35_b200 import check
+    m, n, pad = 130, 70, 3
+    A0 = ol.matgen(35, m + pad, n, dt, dist=2)
+    if beta == 0.0:
+        A0[:m][::7] = np.nan
+    b = beta * (1 - 0.5j) if dt == np.complex128 else beta
+    a = dev(A0)
+    check(te.te_tile_scale(0, stream(), DT[dt], m, n, scalar(b, dt), a.data_ptr(), m + pad))
+    got = host(a, (m + pad, n), dt)
+    want = np.zeros_like(A0[:m]) if beta == 0.0 else b * A0[:m]
+    assert np.allclose(got[:m], want, rtol=4 * EPS, atol=0)
+    assert np.array_equal(got[m:], A0[m:])
