@@ -11,6 +11,10 @@
  *   slate_pdtrsm / slate_pztrsm   scalapack_api/scalapack_trsm.cc
  *   slate_pdsyrk / slate_pzsyrk   scalapack_api/scalapack_syrk.cc
  *   slate_pzherk                  scalapack_api/scalapack_herk.cc
+ *   slate_pdsymm / slate_pzsymm   scalapack_api/scalapack_symm.cc
+ *   slate_pzhemm                  scalapack_api/scalapack_hemm.cc
+ *   slate_pdsyr2k / slate_pzsyr2k scalapack_api/scalapack_syr2k.cc
+ *   slate_pzher2k                 scalapack_api/scalapack_her2k.cc
  *
  * Behaviour kept from the reference: arrays are wrapped in place with fromScaLAPACK (no
  * redistribution), sub-matrix offsets must fall on tile boundaries, SLATE_SCALAPACK_LOOKAHEAD
@@ -82,6 +86,26 @@ void slate_pzsyrk(const char* uplo, const char* trans, int* n, int* k, void* alp
 void slate_pzherk(const char* uplo, const char* trans, int* n, int* k, double* alpha, void* a,
                   int* ia, int* ja, int* desca, double* beta, void* c, int* ic, int* jc,
                   int* descc);
+
+void slate_pdsymm(const char* side, const char* uplo, int* m, int* n, double* alpha, double* a,
+                  int* ia, int* ja, int* desca, double* b, int* ib, int* jb, int* descb, double* beta,
+                  double* c, int* ic, int* jc, int* descc);
+void slate_pzsymm(const char* side, const char* uplo, int* m, int* n, void* alpha, void* a, int* ia,
+                  int* ja, int* desca, void* b, int* ib, int* jb, int* descb, void* beta, void* c,
+                  int* ic, int* jc, int* descc);
+void slate_pzhemm(const char* side, const char* uplo, int* m, int* n, void* alpha, void* a, int* ia,
+                  int* ja, int* desca, void* b, int* ib, int* jb, int* descb, void* beta, void* c,
+                  int* ic, int* jc, int* descc);
+
+void slate_pdsyr2k(const char* uplo, const char* trans, int* n, int* k, double* alpha, double* a,
+                   int* ia, int* ja, int* desca, double* b, int* ib, int* jb, int* descb,
+                   double* beta, double* c, int* ic, int* jc, int* descc);
+void slate_pzsyr2k(const char* uplo, const char* trans, int* n, int* k, void* alpha, void* a, int* ia,
+                   int* ja, int* desca, void* b, int* ib, int* jb, int* descb, void* beta, void* c,
+                   int* ic, int* jc, int* descc);
+void slate_pzher2k(const char* uplo, const char* trans, int* n, int* k, void* alpha, void* a, int* ia,
+                   int* ja, int* desca, void* b, int* ib, int* jb, int* descb, double* beta, void* c,
+                   int* ic, int* jc, int* descc);
 
 #ifdef __cplusplus
 }

@@ -192,6 +192,18 @@ int te_potrf_tile(int device, void* stream, int dtype, int uplo, int n, void* A,
                   int* info_dev, void* scratch, size_t scratch_bytes);
 
 /* ------------------------------------------------------------------------
+ * LU of one tile without pivoting, in place: A (m x n) = L U, L unit lower (m x min(m,n)),
+ * U upper (min(m,n) x n).
+ * Replaces: internal::getrf_nopiv (src/internal/internal_getrf_nopiv.cc, the tile routine of
+ * slate::getrf_nopiv, src/getrf_nopiv.cc:86-95), which the reference runs on the host.
+ * *info_dev = 0, or j if U(j,j) is exactly zero (first such j; the factorisation goes on
+ * without scaling that column).  scratch: te_getrf_nopiv_scratch_bytes(dtype) bytes.
+ * ---------------------------------------------------------------------- */
+size_t te_getrf_nopiv_scratch_bytes(int dtype);
+int te_getrf_nopiv_tile(int device, void* stream, int dtype, int m, int n, void* A, int lda,
+                        int* info_dev, void* scratch, size_t scratch_bytes);
+
+/* ------------------------------------------------------------------------
  * Batched triangular solve with ONE triangular tile A shared by the batch:
  *   side R:  B_i = alpha B_i op(A)^-1   (B_i is m_i x na)
  *   side L:  B_i = alpha op(A)^-1 B_i   (B_i is na x n_i)

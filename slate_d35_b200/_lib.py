@@ -60,6 +60,9 @@ def lib():
     L.te_potrf_scratch_bytes.restype = sz
     L.te_potrf_scratch_bytes.argtypes = [C.c_int]
     L.te_potrf_tile.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, vp, vp, sz]
+    L.te_getrf_nopiv_scratch_bytes.restype = sz
+    L.te_getrf_nopiv_scratch_bytes.argtypes = [C.c_int]
+    L.te_getrf_nopiv_tile.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, vp, vp, sz]
     L.te_trsm_scratch_bytes.restype = sz
     L.te_trsm_scratch_bytes.argtypes = [C.c_int, C.c_int, i64]
     L.te_trsm_batched.argtypes = [C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp,

@@ -460,9 +460,162 @@ static int trsm_batched(int device, cudaStream_t stream, int dtype, int side, in
     return TE_OK;
 }
 
+// ------------------------------- tile LU without pivoting --------------------
+// Reference: src/internal/internal_getrf_nopiv.cc (Tile_getrf_nopiv.hh: recursive LU of the
+// diagonal tile on the host).  Here, like the tile Cholesky: diagonal blocks of IB columns are
+// factored by one CTA in shared memory, everything else is GEMM on the DMMA kernel
+// (L21 = A21 inv(U11), U12 = inv(L11) A12, A22 -= L21 U12, the inverses by the trtri part of
+// potf2_trtri_kernel).
+__device__ __forceinline__ double recip_(double a) { return 1.0 / a; }
+__device__ __forceinline__ zd recip_(zd a)
+{
+    // Smith's formula: no overflow of |a|^2
+    if (fabs(a.x) >= fabs(a.y)) {
+        const double r = a.y / a.x, d = a.x + a.y * r;
+        return make_zd(1.0 / d, -r / d);
+    }
+    const double r = a.x / a.y, d = a.x * r + a.y;
+    return make_zd(r / d, -1.0 / d);
+}
+__device__ __forceinline__ bool is_zero_(double a) { return a == 0.0; }
+__device__ __forceinline__ bool is_zero_(zd a) { return a.x == 0.0 && a.y == 0.0; }
+
+// One CTA: A (n x n, n <= IB) <- L \ U with unit-diagonal L, right-looking, no pivoting.
+// A zero pivot at local column j sets *info = info_base + j + 1 (first one wins) and that
+// column is left unscaled, as LAPACK's unblocked getrf does.
+template <typename T, int IB>
+__global__ void __launch_bounds__(PANEL_THREADS)
+lu_nopiv_block_kernel(T* A, int lda, int n, int* info, int info_base)
+{
+    extern __shared__ __align__(16) unsigned char panel_smem[];
+    T* S = reinterpret_cast<T*>(panel_smem);               // column-major, leading dimension LD
+    constexpr int LD = IB + 1;
+    const int tid = threadIdx.x;
+    for (int idx = tid; idx < n * n; idx += PANEL_THREADS) {
+        const int r = idx % n, c = idx / n;
+        S[r + c * LD] = A[r + (int64_t)c * lda];
+    }
+    __syncthreads();
+    for (int k = 0; k < n; ++k) {
+        const T pivot = S[k + k * LD];
+        const bool singular = is_zero_(pivot);
+        if (singular) {
+            if (tid == 0 && *info == 0) *info = info_base + k + 1;
+        }
+        else {
+            const T rp = recip_(pivot);
+            for (int i = k + 1 + tid; i < n; i += PANEL_THREADS)
+                S[i + k * LD] = S[i + k * LD] * rp;
+        }
+        __syncthreads();
+        const int r = n - k - 1;
+        for (int idx = tid; idx < r * r; idx += PANEL_THREADS) {
+            const int i = k + 1 + idx % r, j = k + 1 + idx / r;
+            S[i + j * LD] = S[i + j * LD] - S[i + k * LD] * S[k + j * LD];
+        }
+        __syncthreads();
+    }
+    for (int idx = tid; idx < n * n; idx += PANEL_THREADS) {
+        const int r = idx % n, c = idx / n;
+        A[r + (int64_t)c * lda] = S[r + c * LD];
+    }
+}
+
+template <typename T>
+static int getrf_nopiv_tile(int device, cudaStream_t stream, int dtype, int m, int n, T* A, int lda,
+                            int* info, T* scratch)
+{
+    constexpr int IB = PanelCfg<T>::IB;
+    int st = configure_panel_kernel<T>(device);
+    if (st != TE_OK) return st;
+    static bool lu_done[64] = {};
+    if (!(device < 64 && lu_done[device])) {
+        TE_CUDA_CHECK(cudaFuncSetAttribute(lu_nopiv_block_kernel<T, IB>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           panel_smem_bytes<T>()));
+        if (device < 64) lu_done[device] = true;
+    }
+    TE_CUDA_CHECK(cudaMemsetAsync(info, 0, sizeof(int), stream));
+    T* invL = scratch;
+    T* invU = scratch + (size_t)IB * IB;
+    const double one[2] = {1.0, 0.0}, zero[2] = {0.0, 0.0}, mone[2] = {-1.0, 0.0};
+    const int mn = m < n ? m : n;
+    for (int jb = 0; jb < mn; jb += IB) {
+        const int ib = (mn - jb < IB) ? mn - jb : IB;
+        T* A11 = A + jb + (int64_t)jb * lda;
+        lu_nopiv_block_kernel<T, IB><<<1, PANEL_THREADS, panel_smem_bytes<T>(), stream>>>(
+            A11, lda, ib, info, jb);
+        te::count_launch();
+        TE_CUDA_CHECK(cudaGetLastError());
+        const int rem_m = m - jb - ib, rem_n = n - jb - ib;
+        if (rem_m <= 0 && rem_n <= 0) break;
+        // inverses of the two factors of the block (trtri-only mode, one CTA each)
+        if (rem_n > 0) {
+            potf2_trtri_kernel<T, IB><<<1, PANEL_THREADS, panel_smem_bytes<T>(), stream>>>(
+                A11, lda, 0, invL, nullptr, 0, 0, 1, 0, 0, ib);
+            te::count_launch();
+        }
+        if (rem_m > 0) {
+            potf2_trtri_kernel<T, IB><<<1, PANEL_THREADS, panel_smem_bytes<T>(), stream>>>(
+                A11, lda, 1, invU, nullptr, 0, 0, 0, 0, 0, ib);
+            te::count_launch();
+        }
+        TE_CUDA_CHECK(cudaGetLastError());
+        te_tile_desc d;
+        d.reserved = 0;
+        d.flags = TE_TILE_GENERAL;
+        T* A21 = A + (jb + ib) + (int64_t)jb * lda;
+        T* A12 = A + jb + (int64_t)(jb + ib) * lda;
+        T* A22 = A + (jb + ib) + (int64_t)(jb + ib) * lda;
+        if (rem_m > 0) {
+            // L21 <- A21 inv(U11)   (in place: a CTA tile spans all ib columns)
+            d.a = A21; d.b = invU; d.c = A21; d.m = rem_m; d.n = ib; d.k = ib;
+            d.lda = lda; d.ldb = IB; d.ldc = lda;
+            st = gemm_inline_any(device, stream, dtype, TE_OP_N, TE_OP_N, one, zero, &d, 1);
+            if (st != TE_OK) return st;
+        }
+        if (rem_n > 0) {
+            // U12 <- inv(L11) A12   (in place: a CTA tile spans all ib rows)
+            d.a = invL; d.b = A12; d.c = A12; d.m = ib; d.n = rem_n; d.k = ib;
+            d.lda = IB; d.ldb = lda; d.ldc = lda;
+            st = gemm_inline_any(device, stream, dtype, TE_OP_N, TE_OP_N, one, zero, &d, 1);
+            if (st != TE_OK) return st;
+        }
+        if (rem_m > 0 && rem_n > 0) {
+            d.a = A21; d.b = A12; d.c = A22; d.m = rem_m; d.n = rem_n; d.k = ib;
+            d.lda = lda; d.ldb = lda; d.ldc = lda;
+            st = gemm_inline_any(device, stream, dtype, TE_OP_N, TE_OP_N, mone, one, &d, 1);
+            if (st != TE_OK) return st;
+        }
+    }
+    return TE_OK;
+}
+
 }  // namespace te
 
 // ------------------------------------ C ABI ------------------------------------
+extern "C" size_t te_getrf_nopiv_scratch_bytes(int dtype)
+{
+    return 2 * (dtype == TE_C64 ? sizeof(te::zd) * 64 * 64 : sizeof(double) * 128 * 128);
+}
+
+extern "C" int te_getrf_nopiv_tile(int device, void* stream, int dtype, int m, int n, void* A, int lda,
+                                   int* info_dev, void* scratch, size_t scratch_bytes)
+{
+    if (!A || !info_dev || !scratch || m < 0 || n < 0 || lda < (m > 1 ? m : 1) ||
+        scratch_bytes < te_getrf_nopiv_scratch_bytes(dtype))
+        return TE_ERR_ARG;
+    int st = te::set_device(device);
+    if (st != TE_OK) return st;
+    if (dtype == TE_F64)
+        return te::getrf_nopiv_tile<double>(device, (cudaStream_t)stream, dtype, m, n, (double*)A, lda,
+                                            info_dev, (double*)scratch);
+    if (dtype == TE_C64)
+        return te::getrf_nopiv_tile<te::zd>(device, (cudaStream_t)stream, dtype, m, n, (te::zd*)A, lda,
+                                            info_dev, (te::zd*)scratch);
+    return TE_ERR_ARG;
+}
+
 extern "C" size_t te_potrf_scratch_bytes(int dtype)
 {
     return dtype == TE_C64 ? sizeof(te::zd) * 64 * 64 : sizeof(double) * 128 * 128;

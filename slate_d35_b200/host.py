@@ -44,6 +44,7 @@ def hostlib():
     L.sb_potrf.argtypes = [vp, C.c_int, C.c_int, C.POINTER(i64), C.POINTER(C.c_float)]
     L.sb_rank_k.argtypes = [C.c_int, C.c_int, dp, vp, dp, vp, C.c_int, C.c_int]
     L.sb_rank_2k.argtypes = [C.c_int, C.c_int, dp, vp, vp, dp, vp, C.c_int, C.c_int]
+    L.sb_getrf_nopiv.argtypes = [vp, C.c_int, C.c_int, C.POINTER(i64)]
     L.sb_hemm.argtypes = [C.c_int, dp, vp, vp, dp, vp, C.c_int, C.c_int]
     L.sb_trsm.argtypes = [C.c_int, C.c_int, dp, vp, vp, C.c_int, C.c_int]
     L.sb_potrs.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.POINTER(i64)]
@@ -52,6 +53,7 @@ def hostlib():
     L.sb_plan_gemm_step.argtypes = [vp, vp, vp, i64, ip, i64, ip]
     L.sb_plan_potrf_step.argtypes = [vp, i64, ip, i64, ip]
     L.sb_plan_gemmA_step.argtypes = [vp, vp, vp, i64, ip, i64, ip]
+    L.sb_plan_getrf_nopiv_step.argtypes = [vp, i64, ip, i64, ip]
     L.sb_tile_rank.argtypes = [vp, i64, i64]
     L.sb_tile_layout.argtypes = [vp, i64, i64]
     L.sb_tile_layout_convert.argtypes = [vp, i64, i64, C.c_int]
@@ -279,6 +281,13 @@ def syr2k(alpha, A, B, beta, Cm, opa="N", lookahead=1, target="D"):
                                 ord(target)))
 
 
+def getrf_nopiv(A, lookahead=1, target="D"):
+    """slate::getrf_nopiv: A = L U in place without pivoting.  Returns info."""
+    info = i64()
+    _check(hostlib().sb_getrf_nopiv(A.h, lookahead, ord(target), C.byref(info)))
+    return info.value
+
+
 def hemm(side, alpha, A, B, beta, Cm, lookahead=1, target="D"):
     """slate::hemm (A a HermitianMatrix) or slate::symm (A a SymmetricMatrix):
     C = alpha A B + beta C (side 'L') or alpha B A + beta C (side 'R')."""
@@ -340,6 +349,16 @@ def plan_gemmA_step(A, B, Cm, k):
     buf = (i64 * cap)()
     used = i64()
     _check(hostlib().sb_plan_gemmA_step(A.h, B.h, Cm.h, k, buf, cap, C.byref(used)))
+    return _unflatten(buf, used.value)
+
+
+def plan_getrf_nopiv_step(A, k):
+    """Broadcasts of LU step k (slate::getrf_nopiv): which = 0 the diagonal tile, 1 the tiles
+    of block column k along their rows, 2 the tiles of block row k down their columns."""
+    cap = 8 * (A.m // A.nb + A.n // A.nb + 8) * (A.p * A.q + 6)
+    buf = (i64 * cap)()
+    used = i64()
+    _check(hostlib().sb_plan_getrf_nopiv_step(A.h, k, buf, cap, C.byref(used)))
     return _unflatten(buf, used.value)
 
 

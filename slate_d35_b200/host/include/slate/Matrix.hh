@@ -259,6 +259,13 @@ public:
     }
 
     /// TriangularMatrix.hh: conversion sharing the tiles (potrf.cc:113-114)
+    /// TriangularMatrix.hh: the uplo triangle of a square general matrix, sharing its tiles
+    /// (getrf_nopiv.cc:104, 137: the L and U factors held in A(k, k))
+    TriangularMatrix(Uplo uplo, Diag diag, Matrix<scalar_t> const& orig)
+        : BaseTrapezoidMatrix<scalar_t>(uplo, orig), diag_(diag)
+    {
+        slate_assert(orig.mt() == orig.nt());
+    }
     TriangularMatrix(Diag diag, BaseTrapezoidMatrix<scalar_t> const& orig)
         : BaseTrapezoidMatrix<scalar_t>(orig), diag_(diag) {}
 

@@ -179,6 +179,21 @@ int64_t potrf(HermitianMatrix<scalar_t>&& A, int priority = 0, int64_t queue_ind
     return potrf(TargetType<Target::Devices>(), A, priority, queue_index, device_info);
 }
 
+// ---- LU without pivoting of one diagonal tile ------------------------------------------------
+/// src/internal/internal.hh getrf_nopiv(A, ib, priority, &info); device_info as for potrf.
+template <typename scalar_t>
+int64_t getrf_nopiv(TargetType<Target::Devices>, Matrix<scalar_t>& A, int64_t ib, int priority,
+                    int64_t queue_index, device_info_int* device_info);
+
+template <Target target = Target::HostTask, typename scalar_t>
+int64_t getrf_nopiv(Matrix<scalar_t>&& A, int64_t ib, int priority = 0, int64_t queue_index = 0,
+                    device_info_int* device_info = nullptr)
+{
+    if (target != Target::Devices)
+        slate_not_implemented("internal::getrf_nopiv: only Target::Devices is built (no CPU fallback)");
+    return getrf_nopiv(TargetType<Target::Devices>(), A, ib, priority, queue_index, device_info);
+}
+
 /// smallest non-zero info over the ranks (src/internal/internal_reduce_info.cc:23-39)
 void reduce_info(int64_t* info, MPI_Comm comm);
 

@@ -61,6 +61,11 @@ template <typename scalar_t>
 void symm(Side side, scalar_t alpha, SymmetricMatrix<scalar_t>& A, Matrix<scalar_t>& B,
           scalar_t beta, Matrix<scalar_t>& C, Options const& opts = Options());
 
+/// LU factorisation without pivoting, A = L U in place, L unit lower (src/getrf_nopiv.cc:26-260).
+/// Returns info: 0, or j if U(j, j) is exactly zero.  Options: Target, Lookahead.
+template <typename scalar_t>
+int64_t getrf_nopiv(Matrix<scalar_t>& A, Options const& opts = Options());
+
 /// Triangular solve with a distributed triangular matrix: op(A) X = alpha B (side L) or
 /// X op(A) = alpha B (side R); src/trsm.cc, src/trsmB.cc, src/work/work_trsm.cc.
 template <typename scalar_t>
@@ -88,6 +93,10 @@ int64_t chol_factor(HermitianMatrix<scalar_t>& A, Options const& opts = Options(
 }
 
 // ---- the broadcast lists of one driver step (shared by the drivers and the planners) -----
+/// src/getrf_nopiv.cc:96-100 (which = 0), 113-120 (1), 178-188 (2): broadcasts of LU step k
+template <typename scalar_t>
+typename Matrix<scalar_t>::BcastListTag getrf_nopiv_bcast_list(int which, Matrix<scalar_t>& A,
+                                                               int64_t k);
 /// src/gemmA.cc:72-78 and :110-118: the broadcast of block column k of B and the reduction of
 /// block column k of C in slate::gemmA
 template <typename scalar_t>

@@ -48,3 +48,19 @@ THREE_NAMES(PZTRSM, pztrsm, TRSM_PARAMS(void), TRSM_ARGS)
 THREE_NAMES(PDSYRK, pdsyrk, RANKK_PARAMS(double, double), RANKK_ARGS)
 THREE_NAMES(PZSYRK, pzsyrk, RANKK_PARAMS(void, void), RANKK_ARGS)
 THREE_NAMES(PZHERK, pzherk, RANKK_PARAMS(double, void), RANKK_ARGS)
+
+#define HEMM_PARAMS(T)                                                                           \
+    (const char* side, const char* uplo, int* m, int* n, T* alpha, T* a, int* ia, int* ja,        \
+     int* da, T* b, int* ib, int* jb, int* db, T* beta, T* c, int* ic, int* jc, int* dc)
+#define HEMM_ARGS (side, uplo, m, n, alpha, a, ia, ja, da, b, ib, jb, db, beta, c, ic, jc, dc)
+THREE_NAMES(PDSYMM, pdsymm, HEMM_PARAMS(double), HEMM_ARGS)
+THREE_NAMES(PZSYMM, pzsymm, HEMM_PARAMS(void), HEMM_ARGS)
+THREE_NAMES(PZHEMM, pzhemm, HEMM_PARAMS(void), HEMM_ARGS)
+
+#define RANK2K_PARAMS(S, T)                                                                      \
+    (const char* uplo, const char* trans, int* n, int* k, T* alpha, T* a, int* ia, int* ja,       \
+     int* da, T* b, int* ib, int* jb, int* db, S* beta, T* c, int* ic, int* jc, int* dc)
+#define RANK2K_ARGS (uplo, trans, n, k, alpha, a, ia, ja, da, b, ib, jb, db, beta, c, ic, jc, dc)
+THREE_NAMES(PDSYR2K, pdsyr2k, RANK2K_PARAMS(double, double), RANK2K_ARGS)
+THREE_NAMES(PZSYR2K, pzsyr2k, RANK2K_PARAMS(void, void), RANK2K_ARGS)
+THREE_NAMES(PZHER2K, pzher2k, RANK2K_PARAMS(double, void), RANK2K_ARGS)

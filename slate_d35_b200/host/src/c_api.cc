@@ -325,6 +325,16 @@ int sb_potrf(void* A, int lookahead, int target, int64_t* info, float* ms)
     });
 }
 
+int sb_getrf_nopiv(void* A, int lookahead, int target, int64_t* info)
+{
+    Handle* h = (Handle*)A;
+    return guarded([&] {
+        Options opts = make_opts(target, lookahead);
+        DISPATCH(h, *info = getrf_nopiv(as_general<double>(h), opts),
+                 *info = getrf_nopiv(as_general<zdouble>(h), opts));
+    });
+}
+
 /// slate::herk (kind = 0; alpha, beta real) or slate::syrk (kind = 1) on op(A)
 int sb_rank_k(int kind, int opa, const double* alpha, void* A, const double* beta, void* C,
               int lookahead, int target)
@@ -466,6 +476,22 @@ int sb_plan_gemmA_step(void* A, void* B, void* C, int64_t k, int64_t* out, int64
             out[pos++] = 2;  out[pos++] = op.i;  out[pos++] = op.j;  out[pos++] = op.root;
             out[pos++] = (int64_t)op.sources.size();
             for (int r : op.sources) out[pos++] = r;
+        }
+        *used = pos;
+    });
+}
+
+/// Broadcasts of LU step k as slate::getrf_nopiv issues them: which = 0 the diagonal tile,
+/// 1 the column tiles along their rows, 2 the row tiles down their columns.
+int sb_plan_getrf_nopiv_step(void* A, int64_t k, int64_t* out, int64_t cap, int64_t* used)
+{
+    Handle* h = (Handle*)A;
+    return guarded([&] {
+        auto& a = as_general<double>(h);
+        int64_t pos = 0;
+        for (int which = 0; which < 3; ++which) {
+            auto l = getrf_nopiv_bcast_list(which, a, k);
+            pos = flatten_plan(a, l, which, out, cap, pos);
         }
         *used = pos;
     });

@@ -548,6 +548,10 @@ void rank_2k_update(bool conjugate, scalar_t alpha, Matrix<scalar_t>& A, Matrix<
         launch_batch<scalar_t>(batch, q, op_left, op_right, pass == 0 ? alpha1 : alpha2,
                                pass == 0 ? beta : scalar_t(1.0));
     }
+    // tileGetForWriting stamped the C tiles with the mark of the first launch; they are final
+    // after the second one (a device-to-host copy of a host-origin C waits for this mark)
+    for (auto const& ij : C_set) C.tileModified(std::get<0>(ij), std::get<1>(ij), device, q);
+    Engine::instance().mark_queue(q);
 }
 }  // namespace
 
@@ -623,7 +627,9 @@ void trsm(TargetType<Target::Devices>, Side side, scalar_t alpha, TriangularMatr
         max_m = std::max(max_m, d.m);
         max_n = std::max(max_n, d.n);
     }
-    const int na = (int)A.tileMb(0);
+    // a triangle cut from a rectangular corner tile (getrf_nopiv at a ragged edge) is the
+    // leading square part of that tile
+    const int na = (int)std::min(A.tileMb(0), A.tileNb(0));
     const int dtype = te_dtype_of<scalar_t>::value;
     size_t bytes = descs.size() * sizeof(te_trsm_desc);
     Engine::DescSlot& slot = eng.acquire_desc(q, bytes);
@@ -673,6 +679,40 @@ int64_t potrf(TargetType<Target::Devices>, HermitianMatrix<scalar_t>& A, int pri
 }
 
 //------------------------------------------------------------------------------
+/// LU without pivoting of one (diagonal) tile, on the device (the reference runs
+/// Tile_getrf_nopiv on the host: src/internal/internal_getrf_nopiv.cc:20-60).  `ib` is
+/// accepted for the signature's sake; the device routine has its own blocking.
+template <typename scalar_t>
+int64_t getrf_nopiv(TargetType<Target::Devices>, Matrix<scalar_t>& A, int64_t ib, int priority,
+                    int64_t queue_index, device_info_int* device_info)
+{
+    slate_assert(A.mt() == 1 && A.nt() == 1);
+    slate_assert(A.op() == Op::NoTrans);
+    if (!A.tileIsLocal(0, 0)) return 0;
+    const int device = 0;
+    const int q = (int)queue_index;
+    Engine& eng = Engine::instance();
+    std::set<ij_tuple> one = {{0, 0}};
+    A.tileGetForWriting(one, device, LayoutConvert::ColMajor, q);
+    auto A00 = A(0, 0, device);
+    const int dtype = te_dtype_of<scalar_t>::value;
+    int* info_dev = device_info ? device_info : eng.info_slot(4095);
+    size_t sb = te_getrf_nopiv_scratch_bytes(dtype);
+    void* scratch = eng.scratch(q, sb);
+    eng.trace_begin(q, "getrf_nopiv_tile", 1);
+    slate_te_call(te_getrf_nopiv_tile(eng.device(), eng.compute_stream(q), dtype, (int)A.tileMb(0),
+                                      (int)A.tileNb(0), A00.data(), (int)A00.stride(), info_dev,
+                                      scratch, sb));
+    eng.trace_end(q);
+    eng.mark_queue(q);
+    if (device_info) return 0;
+    int info = 0;
+    slate_te_call(te_memcpy_async(&info, info_dev, sizeof(int), TE_COPY_D2H, eng.compute_stream(q)));
+    eng.sync_queue(q);
+    return info;
+}
+
+//------------------------------------------------------------------------------
 void reduce_info(int64_t* info, MPI_Comm comm)
 {
     if (!comm || comm->size == 1) return;
@@ -712,7 +752,9 @@ void reduce_info(int64_t* info, MPI_Comm comm)
     template void trsm<T>(TargetType<Target::Devices>, Side, T, TriangularMatrix<T>&,           \
                           Matrix<T>&, int, Layout, int64_t);                                    \
     template int64_t potrf<T>(TargetType<Target::Devices>, HermitianMatrix<T>&, int, int64_t,   \
-                              device_info_int*);
+                              device_info_int*);                                                \
+    template int64_t getrf_nopiv<T>(TargetType<Target::Devices>, Matrix<T>&, int64_t, int,      \
+                                    int64_t, device_info_int*);
 INSTANTIATE(double)
 INSTANTIATE(std::complex<double>)
 

@@ -1,7 +1,8 @@
 // scalapack_api.cc -- ScaLAPACK-convention entry points on the tile engine
 // (include/slate_b200_scalapack.h).
 //
-// What the reference does in scalapack_api/scalapack_{gemm,potrf,potrs,posv,trsm,syrk,herk}.cc:
+// What the reference does in scalapack_api/scalapack_{gemm,potrf,potrs,posv,trsm,syrk,herk,hemm,
+// symm,her2k,syr2k}.cc:
 // read the process grid of the descriptor's BLACS context, wrap the caller's local array
 // with fromScaLAPACK, cut the (ia, ja) sub-matrix at tile boundaries
 // (scalapack_api/scalapack_slate.hh:81-95), apply the op flags as views, call the driver.
@@ -277,6 +278,63 @@ void pherk(const char* uplo, const char* trans, int n, int k, double alpha, T* a
     slate::herk(alpha, A, beta, Cm, call_options());
 }
 
+template <typename T>
+void phemm(bool hermitian, const char* side, const char* uplo, int m, int n, T alpha, T* a, int ia,
+           int ja, const int* desca, T* b, int ib, int jb, const int* descb, T beta, T* c, int ic,
+           int jc, const int* descc)
+{
+    const slate::Side sd = side_of(side);
+    const int64_t an = (sd == slate::Side::Left) ? m : n;
+    auto B = general<T>(m, n, b, ib, jb, descb);
+    auto Cm = general<T>(m, n, c, ic, jc, descc);
+    if (hermitian) {
+        auto A = square<slate::HermitianMatrix<T>>(an, a, ia, ja, desca, uplo_of(uplo));
+        slate_assert(A.mt() == (sd == slate::Side::Left ? Cm.mt() : Cm.nt()));
+        say("hemm");
+        slate::hemm(sd, alpha, A, B, beta, Cm, call_options());
+    }
+    else {
+        auto A = square<slate::SymmetricMatrix<T>>(an, a, ia, ja, desca, uplo_of(uplo));
+        slate_assert(A.mt() == (sd == slate::Side::Left ? Cm.mt() : Cm.nt()));
+        say("symm");
+        slate::symm(sd, alpha, A, B, beta, Cm, call_options());
+    }
+}
+
+template <typename T>
+void psyr2k(const char* uplo, const char* trans, int n, int k, T alpha, T* a, int ia, int ja,
+            const int* desca, T* b, int ib, int jb, const int* descb, T beta, T* c, int ic, int jc,
+            const int* descc)
+{
+    const slate::Op op = op_of(trans);
+    const bool nt = (op == slate::Op::NoTrans);
+    auto A = general<T>(nt ? n : k, nt ? k : n, a, ia, ja, desca);
+    auto B = general<T>(nt ? n : k, nt ? k : n, b, ib, jb, descb);
+    auto Cm = square<slate::SymmetricMatrix<T>>(n, c, ic, jc, descc, uplo_of(uplo));
+    apply_op(A, op);
+    apply_op(B, op);
+    slate_assert(A.mt() == Cm.mt() && B.mt() == Cm.mt() && A.nt() == B.nt());
+    say("syr2k");
+    slate::syr2k(alpha, A, B, beta, Cm, call_options());
+}
+
+template <typename T>
+void pher2k(const char* uplo, const char* trans, int n, int k, T alpha, T* a, int ia, int ja,
+            const int* desca, T* b, int ib, int jb, const int* descb, double beta, T* c, int ic,
+            int jc, const int* descc)
+{
+    const slate::Op op = op_of(trans);
+    const bool nt = (op == slate::Op::NoTrans);
+    auto A = general<T>(nt ? n : k, nt ? k : n, a, ia, ja, desca);
+    auto B = general<T>(nt ? n : k, nt ? k : n, b, ib, jb, descb);
+    auto Cm = square<slate::HermitianMatrix<T>>(n, c, ic, jc, descc, uplo_of(uplo));
+    apply_op(A, op);
+    apply_op(B, op);
+    slate_assert(A.mt() == Cm.mt() && B.mt() == Cm.mt() && A.nt() == B.nt());
+    say("her2k");
+    slate::her2k(alpha, A, B, beta, Cm, call_options());
+}
+
 template <typename F>
 void fortran_call(const char* name, F&& body)
 {
@@ -412,6 +470,62 @@ void slate_pzherk(const char* uplo, const char* trans, int* n, int* k, double* a
     fortran_call("pzherk", [&] {
         pherk<zdouble>(uplo, trans, *n, *k, *alpha, ZP(a), *ia, *ja, desca, *beta, ZP(c), *ic, *jc,
                        descc);
+    });
+}
+
+void slate_pdsymm(const char* side, const char* uplo, int* m, int* n, double* alpha, double* a,
+                  int* ia, int* ja, int* desca, double* b, int* ib, int* jb, int* descb, double* beta,
+                  double* c, int* ic, int* jc, int* descc)
+{
+    fortran_call("pdsymm", [&] {
+        phemm<double>(false, side, uplo, *m, *n, *alpha, a, *ia, *ja, desca, b, *ib, *jb, descb, *beta,
+                      c, *ic, *jc, descc);
+    });
+}
+void slate_pzsymm(const char* side, const char* uplo, int* m, int* n, void* alpha, void* a, int* ia,
+                  int* ja, int* desca, void* b, int* ib, int* jb, int* descb, void* beta, void* c,
+                  int* ic, int* jc, int* descc)
+{
+    fortran_call("pzsymm", [&] {
+        phemm<zdouble>(false, side, uplo, *m, *n, Z(alpha), ZP(a), *ia, *ja, desca, ZP(b), *ib, *jb,
+                       descb, Z(beta), ZP(c), *ic, *jc, descc);
+    });
+}
+void slate_pzhemm(const char* side, const char* uplo, int* m, int* n, void* alpha, void* a, int* ia,
+                  int* ja, int* desca, void* b, int* ib, int* jb, int* descb, void* beta, void* c,
+                  int* ic, int* jc, int* descc)
+{
+    fortran_call("pzhemm", [&] {
+        phemm<zdouble>(true, side, uplo, *m, *n, Z(alpha), ZP(a), *ia, *ja, desca, ZP(b), *ib, *jb,
+                       descb, Z(beta), ZP(c), *ic, *jc, descc);
+    });
+}
+
+void slate_pdsyr2k(const char* uplo, const char* trans, int* n, int* k, double* alpha, double* a,
+                   int* ia, int* ja, int* desca, double* b, int* ib, int* jb, int* descb,
+                   double* beta, double* c, int* ic, int* jc, int* descc)
+{
+    fortran_call("pdsyr2k", [&] {
+        psyr2k<double>(uplo, trans, *n, *k, *alpha, a, *ia, *ja, desca, b, *ib, *jb, descb, *beta, c,
+                       *ic, *jc, descc);
+    });
+}
+void slate_pzsyr2k(const char* uplo, const char* trans, int* n, int* k, void* alpha, void* a, int* ia,
+                   int* ja, int* desca, void* b, int* ib, int* jb, int* descb, void* beta, void* c,
+                   int* ic, int* jc, int* descc)
+{
+    fortran_call("pzsyr2k", [&] {
+        psyr2k<zdouble>(uplo, trans, *n, *k, Z(alpha), ZP(a), *ia, *ja, desca, ZP(b), *ib, *jb, descb,
+                        Z(beta), ZP(c), *ic, *jc, descc);
+    });
+}
+void slate_pzher2k(const char* uplo, const char* trans, int* n, int* k, void* alpha, void* a, int* ia,
+                   int* ja, int* desca, void* b, int* ib, int* jb, int* descb, double* beta, void* c,
+                   int* ic, int* jc, int* descc)
+{
+    fortran_call("pzher2k", [&] {
+        pher2k<zdouble>(uplo, trans, *n, *k, Z(alpha), ZP(a), *ia, *ja, desca, ZP(b), *ib, *jb, descb,
+                        *beta, ZP(c), *ic, *jc, descc);
     });
 }
 

@@ -137,3 +137,36 @@ def pherk(uplo, trans, n, k, alpha, a, ia, ja, desca, beta, c, ic, jc, descc):
     L.slate_pzherk(uplo.encode(), trans.encode(), _i(n), _i(k), _s(alpha, np.float64), _p(a), _i(ia),
                    _i(ja), desca, _s(beta, np.float64), _p(c), _i(ic), _i(jc), descc)
     _finish(L)
+
+
+def phemm(side, uplo, m, n, alpha, a, ia, ja, desca, b, ib, jb, descb, beta, c, ic, jc, descc,
+          hermitian=True):
+    """pzhemm (hermitian, complex only) or p?symm"""
+    L = _lib()
+    name = "slate_pzhemm" if hermitian else f"slate_p{_z(c)}symm"
+    assert not (hermitian and c.dtype != np.complex128)
+    getattr(L, name)(side.encode(), uplo.encode(), _i(m), _i(n), _s(alpha, c.dtype), _p(a), _i(ia),
+                     _i(ja), desca, _p(b), _i(ib), _i(jb), descb, _s(beta, c.dtype), _p(c), _i(ic),
+                     _i(jc), descc)
+    _finish(L)
+
+
+def psymm(*args):
+    return phemm(*args, hermitian=False)
+
+
+def psyr2k(uplo, trans, n, k, alpha, a, ia, ja, desca, b, ib, jb, descb, beta, c, ic, jc, descc):
+    L = _lib()
+    getattr(L, f"slate_p{_z(c)}syr2k")(uplo.encode(), trans.encode(), _i(n), _i(k), _s(alpha, c.dtype),
+                                       _p(a), _i(ia), _i(ja), desca, _p(b), _i(ib), _i(jb), descb,
+                                       _s(beta, c.dtype), _p(c), _i(ic), _i(jc), descc)
+    _finish(L)
+
+
+def pher2k(uplo, trans, n, k, alpha, a, ia, ja, desca, b, ib, jb, descb, beta, c, ic, jc, descc):
+    L = _lib()
+    assert c.dtype == np.complex128
+    L.slate_pzher2k(uplo.encode(), trans.encode(), _i(n), _i(k), _s(alpha, c.dtype), _p(a), _i(ia),
+                    _i(ja), desca, _p(b), _i(ib), _i(jb), descb, _s(beta, np.float64), _p(c), _i(ic),
+                    _i(jc), descc)
+    _finish(L)

@@ -154,6 +154,58 @@ def main():
         want = alpha * A0 @ B20 + beta * C20
         assert np.abs(got - want).max() <= 3 * np.sqrt(k) * EPS * np.abs(want).max()
 
+    # ------------------------------ getrf_nopiv ------------------------------
+    # src/getrf_nopiv.cc: diagonal tile factored by its owner and sent down its column and along
+    # its row; column tiles solved against U and sent along their rows; row tiles solved
+    # against L and sent down their columns; every rank updates its own trailing tiles.
+    def lu_nopiv(a):
+        a = a.copy()
+        for c in range(min(a.shape)):
+            a[c + 1:, c] /= a[c, c]
+            a[c + 1:, c + 1:] -= np.outer(a[c + 1:, c], a[c, c + 1:])
+        return a
+
+    ml, nl, nbl = 45, 38, 8
+    G = sl.Matrix(ml, nl, nbl, p, q, origin="N")
+    G0 = ol.matgen(9, ml, nl)
+    G0[np.arange(min(ml, nl)), np.arange(min(ml, nl))] += max(ml, nl)
+    mtl, ntl = -(-ml // nbl), -(-nl // nbl)
+    g_t = {}
+    for i in range(mtl):
+        for j in range(ntl):
+            if sl.tile_rank(G, i, j) == rank:
+                g_t[(i, j)] = np.asfortranarray(G0[i * nbl:(i + 1) * nbl, j * nbl:(j + 1) * nbl].copy())
+    shape_g = lambda i, j: tile_shape(ml, nl, nbl, i, j)
+    for kk in range(min(mtl, ntl)):
+        ops = sl.plan_getrf_nopiv_step(G, kk)
+        if sl.tile_rank(G, kk, kk) == rank:
+            g_t[(kk, kk)] = np.asfortranarray(lu_nopiv(g_t[(kk, kk)]))
+        run_bcasts(ops, 0, g_t, rank, shape_g)
+        for i in range(kk + 1, mtl):                        # A(i,k) U^-1
+            if sl.tile_rank(G, i, kk) == rank:
+                d = g_t[(kk, kk)]
+                U = np.triu(d[:, :d.shape[1]])[:d.shape[1], :]
+                g_t[(i, kk)] = np.asfortranarray(np.linalg.solve(U.T, g_t[(i, kk)].T).T)
+        run_bcasts(ops, 1, g_t, rank, shape_g)
+        for j in range(kk + 1, ntl):                        # L^-1 A(k,j)
+            if sl.tile_rank(G, kk, j) == rank:
+                d = g_t[(kk, kk)]
+                Lk = np.tril(d[:, :d.shape[0]], -1)[:, :d.shape[0]] + np.eye(d.shape[0])
+                g_t[(kk, j)] = np.asfortranarray(np.linalg.solve(Lk, g_t[(kk, j)]))
+        run_bcasts(ops, 2, g_t, rank, shape_g)
+        for i in range(kk + 1, mtl):
+            for j in range(kk + 1, ntl):
+                if sl.tile_rank(G, i, j) == rank:
+                    g_t[(i, j)] = g_t[(i, j)] - g_t[(i, kk)] @ g_t[(kk, j)]   # KeyError = not delivered
+        for key in [t for t in g_t if (t[0] == kk or t[1] == kk) and sl.tile_rank(G, *t) != rank]:
+            del g_t[key]
+    got = gather_full(g_t, G, ml, nl, nbl, rank, world)
+    if rank == 0:
+        mn = min(ml, nl)
+        Lf = np.tril(got[:, :mn], -1) + np.eye(ml, mn)
+        Uf = np.triu(got[:mn, :])
+        assert np.abs(Lf @ Uf - G0).max() <= 50 * EPS * max(ml, nl) * np.abs(G0).max()
+
     # ------------------------------ potrf ------------------------------
     n, nb = 52, 8
     H = sl.HermitianMatrix("L", n, nb, p, q, origin="N")

@@ -344,7 +344,8 @@ def test_gemm_auto_selects_gemmA_for_one_block_column(sl):
 @pytest.mark.parametrize("uplo", "LU")
 @pytest.mark.parametrize("opa", "NC")
 @pytest.mark.parametrize("dt", [np.float64, np.complex128])
-def test_her2k_syr2k_driver(sl, kind, uplo, opa, dt):
+@pytest.mark.parametrize("origin", "DH")
+def test_her2k_syr2k_driver(sl, kind, uplo, opa, dt, origin):
     """test/test_her2k.cc / test_syr2k.cc scaled down (ragged tiles, complex alpha, both
     triangles, op(A) = A or its (conjugate) transpose); the diagonal of a Hermitian C comes
     back exactly real."""
@@ -357,10 +358,16 @@ def test_her2k_syr2k_driver(sl, kind, uplo, opa, dt):
     C0 = ol.matgen(2, n, n, dt, dist=2)
     if kind == "her2k":
         C0[np.arange(n), np.arange(n)] = C0[np.arange(n), np.arange(n)].real
-    A = sl.Matrix(*ash, nb, dtype=dt).from_numpy(A0)
-    B = sl.Matrix(*ash, nb, dtype=dt).from_numpy(B0)
     cls = sl.HermitianMatrix if kind == "her2k" else sl.SymmetricMatrix
-    Cm = cls(uplo, n, nb, dtype=dt).from_numpy(C0)
+    if origin == "D":
+        A = sl.Matrix(*ash, nb, dtype=dt).from_numpy(A0)
+        B = sl.Matrix(*ash, nb, dtype=dt).from_numpy(B0)
+        Cm = cls(uplo, n, nb, dtype=dt).from_numpy(C0)
+    else:
+        # user-owned host arrays: the result is copied back behind the LAST launch of the update
+        a_h, b_h, c_h = A0.copy(order="F"), B0.copy(order="F"), C0.copy(order="F")
+        A, B = sl.Matrix.fromLAPACK(a_h, nb), sl.Matrix.fromLAPACK(b_h, nb)
+        Cm = cls.fromLAPACK(uplo, c_h, nb)
     Aop, Bop = opn(A0, opa), opn(B0, opa)
     alpha = (-1.25 + 0.5j) if dt == np.complex128 else -1.25
     if kind == "her2k":
@@ -371,7 +378,7 @@ def test_her2k_syr2k_driver(sl, kind, uplo, opa, dt):
         beta = (0.5 - 0.25j) if dt == np.complex128 else 0.5
         sl.syr2k(alpha, A, B, beta, Cm, opa=opa)
         full = alpha * Aop @ Bop.T + alpha * Bop @ Aop.T + beta * C0
-    got = Cm.to_numpy()
+    got = Cm.to_numpy() if origin == "D" else c_h
     tri = np.tril if uplo == "L" else np.triu
     kk = 2 * k * (4 if dt == np.complex128 else 1)
     assert np.abs(tri(got) - tri(full)).max() <= 3 * np.sqrt(kk) * EPS * np.abs(full).max()
@@ -416,6 +423,33 @@ def test_tile_layout_convert_round_trip_and_gemm(sl, dt):
     assert np.array_equal(out[0], out[1])
     want = ALPHA * A0 @ B0 + BETA * C0
     assert np.abs(out[1] - want).max() <= 12 * np.sqrt(k) * EPS * np.abs(want).max()
+
+
+# ------------------------------ getrf_nopiv ------------------------------
+@pytest.mark.parametrize("dt", [np.float64, np.complex128])
+@pytest.mark.parametrize("m,n", [(900, 900), (700, 500), (500, 700), (100, 100)])
+@pytest.mark.parametrize("la", [0, 1, 2])
+def test_getrf_nopiv_driver(sl, dt, m, n, la):
+    """test/test_gesv.cc with the nopiv method, scaled down: ragged tiles, rectangular shapes,
+    several lookahead depths; backward error || A - L U || / (n ||A||)."""
+    nb = 128
+    A0 = ol.matgen(61, m, n, dt, dist=2)
+    mn = min(m, n)
+    A0[np.arange(mn), np.arange(mn)] += max(m, n)
+    A = sl.Matrix(m, n, nb, dtype=dt).from_numpy(A0)
+    assert sl.getrf_nopiv(A, lookahead=la) == 0
+    got = A.to_numpy()
+    Lf = np.tril(got[:, :mn], -1) + np.eye(m, mn)
+    Uf = np.triu(got[:mn, :])
+    assert np.linalg.norm(Lf @ Uf - A0) / (max(m, n) * np.linalg.norm(A0)) <= 50 * EPS
+
+
+def test_getrf_nopiv_info(sl):
+    n, nb = 600, 128
+    A0 = np.asfortranarray(np.eye(n) * 3.0 + np.triu(np.ones((n, n)), 1))
+    A0[333, 333] = 0.0
+    A = sl.Matrix(n, n, nb).from_numpy(A0)
+    assert sl.getrf_nopiv(A) == 334
 
 
 # ------------------------------ hemm / symm (SURVEY 8f, item 3) ------------------------------

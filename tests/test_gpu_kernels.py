@@ -459,3 +459,45 @@ def test_tile_scale(te, dt, beta):
     want = np.zeros_like(A0[:m]) if beta == 0.0 else b * A0[:m]
     assert np.allclose(got[:m], want, rtol=4 * EPS, atol=0)
     assert np.array_equal(got[m:], A0[m:])
+
+
+# ------------------------------ tile LU without pivoting ------------------------------
+@pytest.mark.parametrize("dt", [np.float64, np.complex128])
+@pytest.mark.parametrize("m,n,pad", [(512, 512, 0), (300, 300, 5), (130, 130, 0), (64, 64, 1), (40, 40, 0),
+                                     (384, 256, 0), (256, 384, 3), (1, 1, 0)])
+def test_getrf_nopiv_tile(te, dt, m, n, pad):
+    """te_getrf_nopiv_tile (replaces the host tile routine of internal::getrf_nopiv):
+    L U = A on a diagonally dominant tile, square and rectangular, padding untouched."""
+    import torch
+    from slate_d35_b200 import check
+    A0 = ol.matgen(51, m + pad, n, dt, dist=2)
+    mn = min(m, n)
+    A0[np.arange(mn), np.arange(mn)] += max(m, n)
+    a = dev(A0)
+    info = torch.full((1,), -7, dtype=torch.int32, device="cuda")
+    sb = te.te_getrf_nopiv_scratch_bytes(DT[dt])
+    scratch = torch.empty(sb, dtype=torch.uint8, device="cuda")
+    check(te.te_getrf_nopiv_tile(0, stream(), DT[dt], m, n, a.data_ptr(), m + pad, info.data_ptr(),
+                                 scratch.data_ptr(), sb))
+    got = host(a, (m + pad, n), dt)
+    assert int(info.item()) == 0
+    Lf = np.tril(got[:m, :mn], -1) + np.eye(m, mn)
+    Uf = np.triu(got[:mn, :])
+    assert np.abs(Lf @ Uf - A0[:m]).max() <= 30 * EPS * max(m, n) * np.abs(A0[:m]).max()
+    assert np.array_equal(got[m:], A0[m:])
+
+
+def test_getrf_nopiv_tile_zero_pivot(te):
+    """an exactly zero pivot is reported (first one), as LAPACK's unblocked LU does"""
+    import torch
+    from slate_d35_b200 import check
+    n = 200
+    A0 = np.asfortranarray(np.eye(n) * 3.0 + np.triu(np.ones((n, n)), 1))
+    A0[141, 141] = 0.0
+    a = dev(A0)
+    info = torch.zeros(1, dtype=torch.int32, device="cuda")
+    sb = te.te_getrf_nopiv_scratch_bytes(0)
+    scratch = torch.empty(sb, dtype=torch.uint8, device="cuda")
+    check(te.te_getrf_nopiv_tile(0, stream(), 0, n, n, a.data_ptr(), n, info.data_ptr(), scratch.data_ptr(), sb))
+    torch.cuda.synchronize()
+    assert int(info.item()) == 142

@@ -176,6 +176,56 @@ def test_psyrk_pherk(sc, uplo, trans):
     assert not np.diag(h).imag.any()
 
 
+@pytest.mark.parametrize("side", "LR")
+@pytest.mark.parametrize("uplo", "LU")
+def test_psymm_phemm(sc, side, uplo):
+    m, n, nb = 512, 384, 128
+    an = m if side == "L" else n
+    tri = np.tril if uplo == "L" else np.triu
+    for herm, dt in ((False, np.float64), (False, np.complex128), (True, np.complex128)):
+        A0 = ol.matgen(21, an, an, dt)
+        S = (A0 + (A0.conj().T if herm else A0.T)) / 2
+        B0, C0 = ol.matgen(22, m, n, dt), ol.matgen(23, m, n, dt)
+        c = padded(C0)
+        alpha, beta = ((1.5 - 0.5j), (0.25 + 2j)) if dt == np.complex128 else (3.0, -0.5)
+        sc.phemm(side, uplo, m, n, alpha, np.asfortranarray(tri(S)), 1, 1, sc.descinit(an, an, nb, nb, CTXT, an),
+                 np.asfortranarray(B0), 1, 1, sc.descinit(m, n, nb, nb, CTXT, m), beta,
+                 c, 1, 1, sc.descinit(m, n, nb, nb, CTXT, c.shape[0]), hermitian=herm)
+        want = alpha * (S @ B0 if side == "L" else B0 @ S) + beta * C0
+        assert np.abs(c[:m] - want).max() <= 12 * np.sqrt(an) * EPS * np.abs(want).max()
+        assert not c[m:].any()
+
+
+@pytest.mark.parametrize("uplo", "LU")
+@pytest.mark.parametrize("trans", "NT")
+def test_psyr2k_pher2k(sc, uplo, trans):
+    n, k, nb = 512, 256, 128
+    tri = np.tril if uplo == "L" else np.triu
+    ash = (n, k) if trans == "N" else (k, n)
+    for herm, dt in ((False, np.float64), (False, np.complex128), (True, np.complex128)):
+        tr = ("N" if trans == "N" else "C") if herm else trans
+        A0, B0, C0 = ol.matgen(24, *ash, dt), ol.matgen(25, *ash, dt), ol.matgen(26, n, n, dt)
+        if herm:
+            C0 = (C0 + C0.conj().T) / 2
+        c = np.asfortranarray(C0.copy())
+        alpha = (1.5 - 0.5j) if dt == np.complex128 else 3.0
+        da = sc.descinit(*ash, nb, nb, CTXT, ash[0])
+        dc = sc.descinit(n, n, nb, nb, CTXT, n)
+        Aop, Bop = op(A0, tr), op(B0, tr)
+        if herm:
+            sc.pher2k(uplo, tr, n, k, alpha, np.asfortranarray(A0), 1, 1, da, np.asfortranarray(B0), 1, 1, da,
+                      -0.5, c, 1, 1, dc)
+            want = alpha * Aop @ Bop.conj().T + np.conj(alpha) * Bop @ Aop.conj().T - 0.5 * C0
+        else:
+            beta = (0.25 + 2j) if dt == np.complex128 else -0.5
+            sc.psyr2k(uplo, tr, n, k, alpha, np.asfortranarray(A0), 1, 1, da, np.asfortranarray(B0), 1, 1, da,
+                      beta, c, 1, 1, dc)
+            want = alpha * Aop @ Bop.T + alpha * Bop @ Aop.T + beta * C0
+        assert np.abs(tri(c) - tri(want)).max() <= 12 * np.sqrt(2 * k) * EPS * np.abs(want).max()
+        other = (lambda x: np.triu(x, 1)) if uplo == "L" else (lambda x: np.tril(x, -1))
+        assert np.array_equal(other(c), other(C0))
+
+
 def test_errors_are_loud(sc, monkeypatch):
     nb = 64
     a = np.zeros((128, 128), order="F")
