@@ -165,6 +165,44 @@ def main():
             for M in (A, B, Cm):
                 M.free()
 
+    # hemm / symm, her2k and getrf_nopiv on the grids (their broadcast plans run over gloo in
+    # tests/mp_worker.py; this is the same on GPUs over NCCL)
+    for (p, q) in GRIDS[world]:
+        n, nrhs, nb = 1500, 700, 256
+        S0 = ol.matgen(30, n, n)
+        S0 = (S0 + S0.T) / 2
+        B0, C0 = ol.matgen(31, n, nrhs), ol.matgen(32, n, nrhs)
+        H = sl.HermitianMatrix("L", n, nb, p, q).from_numpy(np.tril(S0))
+        B = sl.Matrix(n, nrhs, nb, p, q).from_numpy(B0)
+        Cm = sl.Matrix(n, nrhs, nb, p, q).from_numpy(C0)
+        sl.hemm("L", 3.0, H, B, -0.5, Cm)
+        got = assemble(Cm)
+        herr = np.abs(got - (3.0 * S0 @ B0 - 0.5 * C0)).max() / np.abs(S0 @ B0).max()
+
+        K0, L0 = ol.matgen(33, n, nrhs), ol.matgen(34, n, nrhs)
+        Ak = sl.Matrix(n, nrhs, nb, p, q).from_numpy(K0)
+        Bk = sl.Matrix(n, nrhs, nb, p, q).from_numpy(L0)
+        Ck = sl.HermitianMatrix("L", n, nb, p, q).from_numpy(np.tril(S0))
+        sl.her2k(2.0, Ak, Bk, 1.0, Ck)
+        got = assemble(Ck)
+        want = 2.0 * (K0 @ L0.T + L0 @ K0.T) + S0
+        kerr = np.abs(np.tril(got) - np.tril(want)).max() / np.abs(want).max()
+
+        G0 = ol.matgen(35, n, n)
+        G0[np.arange(n), np.arange(n)] += n
+        G = sl.Matrix(n, n, nb, p, q).from_numpy(G0)
+        info = sl.getrf_nopiv(G)
+        got = assemble(G)
+        Lf, Uf = np.tril(got, -1) + np.eye(n), np.triu(got)
+        lerr = np.linalg.norm(Lf @ Uf - G0) / (n * np.linalg.norm(G0))
+        if rank == 0:
+            ok = herr <= 3 * np.sqrt(n) * EPS and kerr <= 3 * np.sqrt(2 * nrhs) * EPS and info == 0 and lerr <= 50 * EPS
+            fails += (not ok)
+            print(f"hemm/her2k/getrf_nopiv {p}x{q}: hemm err {herr:.2e}, her2k err {kerr:.2e}, "
+                  f"LU info {info} backward {lerr:.2e} {'ok' if ok else 'FAIL'}", flush=True)
+        for M in (H, B, Cm, Ak, Bk, Ck, G):
+            M.free()
+
     # the ScaLAPACK-convention entry points (include/slate_b200_scalapack.h) as an unmodified
     # ScaLAPACK program calls them: pdgemm (with transposes) and pdposv on both rank orders
     from slate_d35_b200 import scalapack as sc

@@ -54,6 +54,7 @@ def hostlib():
     L.sb_plan_potrf_step.argtypes = [vp, i64, ip, i64, ip]
     L.sb_plan_gemmA_step.argtypes = [vp, vp, vp, i64, ip, i64, ip]
     L.sb_plan_getrf_nopiv_step.argtypes = [vp, i64, ip, i64, ip]
+    L.sb_plan_hemm_step.argtypes = [vp, vp, vp, i64, ip, i64, ip]
     L.sb_tile_rank.argtypes = [vp, i64, i64]
     L.sb_tile_layout.argtypes = [vp, i64, i64]
     L.sb_tile_layout_convert.argtypes = [vp, i64, i64, C.c_int]
@@ -349,6 +350,16 @@ def plan_gemmA_step(A, B, Cm, k):
     buf = (i64 * cap)()
     used = i64()
     _check(hostlib().sb_plan_gemmA_step(A.h, B.h, Cm.h, k, buf, cap, C.byref(used)))
+    return _unflatten(buf, used.value)
+
+
+def plan_hemm_step(A, B, Cm, k):
+    """Broadcasts of step k of slate::hemm, side Left: which = 0 the tiles standing for block
+    column k of the Hermitian A, 1 block row k of B."""
+    cap = 8 * (Cm.m // Cm.nb + Cm.n // Cm.nb + 8) * (Cm.p * Cm.q + 6)
+    buf = (i64 * cap)()
+    used = i64()
+    _check(hostlib().sb_plan_hemm_step(A.h, B.h, Cm.h, k, buf, cap, C.byref(used)))
     return _unflatten(buf, used.value)
 
 

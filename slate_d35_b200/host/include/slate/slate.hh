@@ -93,6 +93,11 @@ int64_t chol_factor(HermitianMatrix<scalar_t>& A, Options const& opts = Options(
 }
 
 // ---- the broadcast lists of one driver step (shared by the drivers and the planners) -----
+/// src/hemmC.cc:98-137: the broadcasts of step k of hemm / symm, side Left (which = 0: tiles
+/// of A, 1: block row k of B)
+template <typename scalar_t, typename AMatrix>
+typename Matrix<scalar_t>::BcastListTag hemm_bcast_list(int which, AMatrix& A, Matrix<scalar_t>& B,
+                                                        Matrix<scalar_t>& C, int64_t k);
 /// src/getrf_nopiv.cc:96-100 (which = 0), 113-120 (1), 178-188 (2): broadcasts of LU step k
 template <typename scalar_t>
 typename Matrix<scalar_t>::BcastListTag getrf_nopiv_bcast_list(int which, Matrix<scalar_t>& A,

@@ -481,6 +481,20 @@ int sb_plan_gemmA_step(void* A, void* B, void* C, int64_t k, int64_t* out, int64
     });
 }
 
+/// Broadcasts of step k of slate::hemm (side Left): which = 0 tiles of A, 1 block row k of B.
+int sb_plan_hemm_step(void* A, void* B, void* C, int64_t k, int64_t* out, int64_t cap, int64_t* used)
+{
+    Handle *ha = (Handle*)A, *hb = (Handle*)B, *hc = (Handle*)C;
+    return guarded([&] {
+        auto& a = as_herm<double>(ha);  auto& b = as_general<double>(hb);
+        auto& c = as_general<double>(hc);
+        auto la = hemm_bcast_list<double>(0, a, b, c, k);
+        auto lb = hemm_bcast_list<double>(1, a, b, c, k);
+        int64_t pos = flatten_plan(a, la, 0, out, cap, 0);
+        *used = flatten_plan(b, lb, 1, out, cap, pos);
+    });
+}
+
 /// Broadcasts of LU step k as slate::getrf_nopiv issues them: which = 0 the diagonal tile,
 /// 1 the column tiles along their rows, 2 the row tiles down their columns.
 int sb_plan_getrf_nopiv_step(void* A, int64_t k, int64_t* out, int64_t cap, int64_t* used)

@@ -20,6 +20,30 @@
 
 namespace slate {
 
+/// Broadcasts of step k of slate::hemm / symm, side Left (src/hemmC.cc:98-137):
+/// which = 0: the tile standing for A(i, k) -- (i, k) where the triangle stores it, (k, i)
+/// where it does not -- to the owners of block row i of C; which = 1: B(k, j) to the owners of
+/// block column j of C.
+template <typename scalar_t, typename AMatrix>
+typename Matrix<scalar_t>::BcastListTag hemm_bcast_list(int which, AMatrix& A, Matrix<scalar_t>& B,
+                                                        Matrix<scalar_t>& C, int64_t k)
+{
+    typename Matrix<scalar_t>::BcastListTag list;
+    const int64_t mt = C.mt(), nt = C.nt();
+    const bool lower = (A.uploLogical() == Uplo::Lower);
+    if (which == 0) {
+        for (int64_t i = 0; i < mt; ++i) {
+            const bool direct = (i == k) || (lower ? i > k : i < k);
+            list.push_back({direct ? i : k, direct ? k : i, {C.sub(i, i, 0, nt - 1)}, i});
+        }
+    }
+    else {
+        for (int64_t j = 0; j < nt; ++j)
+            list.push_back({k, j, {C.sub(0, mt - 1, j, j)}, j});
+    }
+    return list;
+}
+
 namespace {
 
 template <typename scalar_t, typename AMatrix>
@@ -65,14 +89,9 @@ void hemm_symm(bool hermitian, Side side, scalar_t alpha, AMatrix A, Matrix<scal
     auto stored = [&](int64_t i, int64_t k) { return lower ? i > k : i < k; };
 
     auto bcast = [&](int64_t k) {
-        BcastListTag list_A, list_B;
-        for (int64_t i = 0; i < mt; ++i) {
-            const bool direct = (i == k) || stored(i, k);
-            list_A.push_back({direct ? i : k, direct ? k : i, {C.sub(i, i, 0, nt - 1)}, i});
-        }
+        BcastListTag list_A = hemm_bcast_list<scalar_t>(0, A, B, C, k);
         A.template listBcastMT<Target::Devices>(list_A, layout);
-        for (int64_t j = 0; j < nt; ++j)
-            list_B.push_back({k, j, {C.sub(0, mt - 1, j, j)}, j});
+        BcastListTag list_B = hemm_bcast_list<scalar_t>(1, A, B, C, k);
         B.template listBcastMT<Target::Devices>(list_B, layout);
     };
     for (int64_t k = 0; k <= lookahead && k < mt; ++k)
@@ -143,6 +162,10 @@ void symm(Side side, scalar_t alpha, SymmetricMatrix<scalar_t>& A, Matrix<scalar
 }
 
 #define INSTANTIATE(T)                                                                          \
+    template typename Matrix<T>::BcastListTag hemm_bcast_list<T, HermitianMatrix<T>>(             \
+        int, HermitianMatrix<T>&, Matrix<T>&, Matrix<T>&, int64_t);                             \
+    template typename Matrix<T>::BcastListTag hemm_bcast_list<T, SymmetricMatrix<T>>(             \
+        int, SymmetricMatrix<T>&, Matrix<T>&, Matrix<T>&, int64_t);                             \
     template void hemm<T>(Side, T, HermitianMatrix<T>&, Matrix<T>&, T, Matrix<T>&, Options const&); \
     template void symm<T>(Side, T, SymmetricMatrix<T>&, Matrix<T>&, T, Matrix<T>&, Options const&);
 INSTANTIATE(double)

@@ -206,6 +206,46 @@ def main():
         Uf = np.triu(got[:mn, :])
         assert np.abs(Lf @ Uf - G0).max() <= 50 * EPS * max(ml, nl) * np.abs(G0).max()
 
+    # ------------------------------ hemm (side Left, lower storage) ------------------------------
+    # src/hemmC.cc: block column k of the Hermitian A is read from the stored triangle where it
+    # exists and as the transposed block row where it does not; both travel to the owners of
+    # the block rows of C.
+    nh, nn, nbh = 43, 21, 8
+    Hh = sl.HermitianMatrix("L", nh, nbh, p, q, origin="N")
+    Bh = sl.Matrix(nh, nn, nbh, p, q, origin="N")
+    Ch = sl.Matrix(nh, nn, nbh, p, q, origin="N")
+    S0 = ol.matgen(10, nh, nh)
+    S0 = (S0 + S0.T) / 2
+    Bh0, Ch0 = ol.matgen(11, nh, nn), ol.matgen(12, nh, nn)
+    mth, nth = -(-nh // nbh), -(-nn // nbh)
+    s_t = {(i, j): np.asfortranarray(S0[i * nbh:(i + 1) * nbh, j * nbh:(j + 1) * nbh].copy())
+           for i in range(mth) for j in range(i + 1) if sl.tile_rank(Hh, i, j) == rank}
+    bh_t = {(i, j): np.asfortranarray(Bh0[i * nbh:(i + 1) * nbh, j * nbh:(j + 1) * nbh].copy())
+            for i in range(mth) for j in range(nth) if sl.tile_rank(Bh, i, j) == rank}
+    ch_t = {(i, j): np.asfortranarray(Ch0[i * nbh:(i + 1) * nbh, j * nbh:(j + 1) * nbh].copy())
+            for i in range(mth) for j in range(nth) if sl.tile_rank(Ch, i, j) == rank}
+    for kk in range(mth):
+        ops = sl.plan_hemm_step(Hh, Bh, Ch, kk)
+        run_bcasts(ops, 0, s_t, rank, lambda i, j: tile_shape(nh, nh, nbh, i, j))
+        run_bcasts(ops, 1, bh_t, rank, lambda i, j: tile_shape(nh, nn, nbh, i, j))
+        for (i, j), c in ch_t.items():
+            if i == kk:
+                d = s_t[(kk, kk)]
+                a_ik = np.tril(d) + np.tril(d, -1).T
+            elif i > kk:
+                a_ik = s_t[(i, kk)]
+            else:
+                a_ik = s_t[(kk, i)].T
+            ch_t[(i, j)] = alpha * a_ik @ bh_t[(kk, j)] + (beta if kk == 0 else 1.0) * c
+        for key in [t for t in s_t if (t[1] == kk or t[0] == kk) and sl.tile_rank(Hh, *t) != rank]:
+            del s_t[key]
+        for key in [t for t in bh_t if t[0] == kk and sl.tile_rank(Bh, *t) != rank]:
+            del bh_t[key]
+    got = gather_full(ch_t, Ch, nh, nn, nbh, rank, world)
+    if rank == 0:
+        want = alpha * S0 @ Bh0 + beta * Ch0
+        assert np.abs(got - want).max() <= 3 * np.sqrt(nh) * EPS * np.abs(want).max()
+
     # ------------------------------ potrf ------------------------------
     n, nb = 52, 8
     H = sl.HermitianMatrix("L", n, nb, p, q, origin="N")
