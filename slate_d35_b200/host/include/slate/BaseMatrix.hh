@@ -226,13 +226,13 @@ public:
     {
         for (auto const& ij : tiles) tileGet(std::get<0>(ij), std::get<1>(ij), device, false, queue);
         finishSet(device, queue);
-        if (device != HostNum && lc != LayoutConvert::None)
+        if (device != HostNum && lc != LayoutConvert::None && storage_->any_rowmajor_)
             for (auto const& ij : tiles) convertIfNeeded(std::get<0>(ij), std::get<1>(ij), device, lc, queue);
     }
     void tileGetForWriting(std::set<ij_tuple>& tiles, int device,
                            LayoutConvert lc = LayoutConvert::None, int queue = -1)
     {
-        if (device != HostNum && lc != LayoutConvert::None) {
+        if (device != HostNum && lc != LayoutConvert::None && storage_->any_rowmajor_) {
             // conversions first (see the single-tile overload)
             bool any = false;
             for (auto const& ij : tiles)
@@ -509,14 +509,14 @@ protected:
     /// true if tile (i, j) has a valid device instance in the other layout
     bool needsConvert(int64_t i, int64_t j, LayoutConvert lc)
     {
-        if (lc == LayoutConvert::None) return false;
+        if (lc == LayoutConvert::None || !storage_->any_rowmajor_) return false;
         auto* node = storage_->find(globalIndex(i, j));
         return node && node->dev && node->dev_state != MOSI::Invalid
                && node->dev->layout() != Layout(char(lc));
     }
     void convertIfNeeded(int64_t i, int64_t j, int device, LayoutConvert lc, int queue)
     {
-        if (lc == LayoutConvert::None) return;
+        if (lc == LayoutConvert::None || !storage_->any_rowmajor_) return;
         auto* node = storage_->find(globalIndex(i, j));
         if (node && node->dev && node->dev_state != MOSI::Invalid
             && node->dev->layout() != Layout(char(lc)))
@@ -714,6 +714,7 @@ void BaseMatrix<scalar_t>::tileLayoutConvert(int64_t i, int64_t j, int device, L
     Tile<scalar_t>* t = node.dev;
     slate_assert(t != nullptr && node.dev_state != MOSI::Invalid);
     if (t->layout() == layout) return;
+    if (layout == Layout::RowMajor) storage_->any_rowmajor_ = true;
     const int dtype = is_complex ? TE_C64 : TE_F64;
     // stored array now: rows x cols column-major
     const bool col = (t->layout() == Layout::ColMajor);

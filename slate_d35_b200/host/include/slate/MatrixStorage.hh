@@ -149,6 +149,10 @@ public:
 
     /// A pool block used as scratch by enqueued work (listReduce receive buffers): returned
     /// with the next flushErased().
+    /// set once a device tile of this matrix has been converted to RowMajor: until then the
+    /// layout checks of tileGetForReading / Writing are skipped (they cost a map lookup per tile)
+    bool any_rowmajor_ = false;
+
     void* allocScratchBlock() { return memory_.alloc(0, memory_.block_size()); }
     void freeDeferred(void* block) { pending_free_.push_back(block); }
 
