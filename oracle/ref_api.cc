@@ -186,6 +186,148 @@ int64_t ref_internal_potrf(int uplo, int64_t n, T* A, int64_t lda)
     }
 }
 
+// ---- the drivers of SURVEY.md section 8f, through the reference's own public functions ----
+template <typename T> T scalar_of(const double* v);
+template <> double scalar_of<double>(const double* v) { return v[0]; }
+template <> zdouble scalar_of<zdouble>(const double* v) { return zdouble(v[0], v[1]); }
+
+inline Uplo uplo_of(int c) { return c == 'U' ? Uplo::Upper : Uplo::Lower; }
+inline slate::Side side_of(int c) { return c == 'R' ? slate::Side::Right : slate::Side::Left; }
+
+template <typename F>
+int64_t guarded(const char* name, F&& f)
+{
+    try { return f(); }
+    catch (std::exception const& e) {
+        fprintf(stderr, "%s: %s\n", name, e.what());
+        return -1000000;
+    }
+}
+
+// kind 0: slate::herk (src/herk.cc), 1: slate::syrk (src/syrk.cc); op(A) is n x k
+template <typename T>
+int64_t ref_rank_k(int kind, int uplo, int opa, int64_t n, int64_t k, int64_t nb, const double* alpha,
+                   T* A, int64_t lda, const double* beta, T* C, int64_t ldc, int la)
+{
+    return guarded("ref_rank_k", [&]() -> int64_t {
+        int64_t am = (opa == 'N') ? n : k, an = (opa == 'N') ? k : n;
+        auto Am = slate::Matrix<T>::fromLAPACK(am, an, A, lda, nb, 1, 1, MPI_COMM_WORLD);
+        auto opA = apply_op(Am, opa);
+        if (kind == 0) {
+            auto Cm = slate::HermitianMatrix<T>::fromLAPACK(uplo_of(uplo), n, C, ldc, nb, 1, 1, MPI_COMM_WORLD);
+            slate::herk(alpha[0], opA, beta[0], Cm, host_opts(la));
+        }
+        else {
+            auto Cm = slate::SymmetricMatrix<T>::fromLAPACK(uplo_of(uplo), n, C, ldc, nb, 1, 1, MPI_COMM_WORLD);
+            slate::syrk(scalar_of<T>(alpha), opA, scalar_of<T>(beta), Cm, host_opts(la));
+        }
+        return 0;
+    });
+}
+
+// kind 0: slate::her2k (src/her2k.cc), 1: slate::syr2k (src/syr2k.cc)
+template <typename T>
+int64_t ref_rank_2k(int kind, int uplo, int opa, int64_t n, int64_t k, int64_t nb, const double* alpha,
+                    T* A, int64_t lda, T* B, int64_t ldb, const double* beta, T* C, int64_t ldc, int la)
+{
+    return guarded("ref_rank_2k", [&]() -> int64_t {
+        int64_t am = (opa == 'N') ? n : k, an = (opa == 'N') ? k : n;
+        auto Am = slate::Matrix<T>::fromLAPACK(am, an, A, lda, nb, 1, 1, MPI_COMM_WORLD);
+        auto Bm = slate::Matrix<T>::fromLAPACK(am, an, B, ldb, nb, 1, 1, MPI_COMM_WORLD);
+        auto opA = apply_op(Am, opa);
+        auto opB = apply_op(Bm, opa);
+        if (kind == 0) {
+            auto Cm = slate::HermitianMatrix<T>::fromLAPACK(uplo_of(uplo), n, C, ldc, nb, 1, 1, MPI_COMM_WORLD);
+            slate::her2k(scalar_of<T>(alpha), opA, opB, beta[0], Cm, host_opts(la));
+        }
+        else {
+            auto Cm = slate::SymmetricMatrix<T>::fromLAPACK(uplo_of(uplo), n, C, ldc, nb, 1, 1, MPI_COMM_WORLD);
+            slate::syr2k(scalar_of<T>(alpha), opA, opB, scalar_of<T>(beta), Cm, host_opts(la));
+        }
+        return 0;
+    });
+}
+
+// kind 0: slate::hemm (src/hemm.cc -> hemmC / hemmA), 1: slate::symm (src/symm.cc)
+template <typename T>
+int64_t ref_hemm(int kind, int side, int uplo, int64_t m, int64_t n, int64_t nb, const double* alpha,
+                 T* A, int64_t lda, T* B, int64_t ldb, const double* beta, T* C, int64_t ldc, int la)
+{
+    return guarded("ref_hemm", [&]() -> int64_t {
+        int64_t an = (side == 'R') ? n : m;
+        auto Bm = slate::Matrix<T>::fromLAPACK(m, n, B, ldb, nb, 1, 1, MPI_COMM_WORLD);
+        auto Cm = slate::Matrix<T>::fromLAPACK(m, n, C, ldc, nb, 1, 1, MPI_COMM_WORLD);
+        if (kind == 0) {
+            auto Am = slate::HermitianMatrix<T>::fromLAPACK(uplo_of(uplo), an, A, lda, nb, 1, 1, MPI_COMM_WORLD);
+            slate::hemm(side_of(side), scalar_of<T>(alpha), Am, Bm, scalar_of<T>(beta), Cm, host_opts(la));
+        }
+        else {
+            auto Am = slate::SymmetricMatrix<T>::fromLAPACK(uplo_of(uplo), an, A, lda, nb, 1, 1, MPI_COMM_WORLD);
+            slate::symm(side_of(side), scalar_of<T>(alpha), Am, Bm, scalar_of<T>(beta), Cm, host_opts(la));
+        }
+        return 0;
+    });
+}
+
+// slate::trsm (src/trsm.cc -> trsmB / trsmA, src/work/work_trsm.cc)
+template <typename T>
+int64_t ref_trsm(int side, int uplo, int opa, int diag, int64_t m, int64_t n, int64_t nb,
+                 const double* alpha, T* A, int64_t lda, T* B, int64_t ldb, int la)
+{
+    return guarded("ref_trsm", [&]() -> int64_t {
+        int64_t an = (side == 'R') ? n : m;
+        auto Am = slate::TriangularMatrix<T>::fromLAPACK(
+            uplo_of(uplo), diag == 'U' ? slate::Diag::Unit : slate::Diag::NonUnit, an, A, lda, nb, 1, 1,
+            MPI_COMM_WORLD);
+        auto Bm = slate::Matrix<T>::fromLAPACK(m, n, B, ldb, nb, 1, 1, MPI_COMM_WORLD);
+        auto opA = apply_op(Am, opa);
+        slate::trsm(side_of(side), scalar_of<T>(alpha), opA, Bm, host_opts(la));
+        return 0;
+    });
+}
+
+// slate::posv (src/posv.cc): factor and solve; returns info
+template <typename T>
+int64_t ref_posv(int uplo, int64_t n, int64_t nrhs, int64_t nb, T* A, int64_t lda, T* B, int64_t ldb,
+                 int la)
+{
+    return guarded("ref_posv", [&]() -> int64_t {
+        auto Am = slate::HermitianMatrix<T>::fromLAPACK(uplo_of(uplo), n, A, lda, nb, 1, 1, MPI_COMM_WORLD);
+        auto Bm = slate::Matrix<T>::fromLAPACK(n, nrhs, B, ldb, nb, 1, 1, MPI_COMM_WORLD);
+        return slate::posv(Am, Bm, host_opts(la));
+    });
+}
+
+// slate::gemm forced onto gemmA (src/gemmA.cc) by Option::MethodGemm
+template <typename T>
+int64_t ref_gemmA(int opa, int opb, int64_t m, int64_t n, int64_t k, int64_t nb, const double* alpha,
+                  T* A, int64_t lda, T* B, int64_t ldb, const double* beta, T* C, int64_t ldc, int la)
+{
+    return guarded("ref_gemmA", [&]() -> int64_t {
+        int64_t am = (opa == 'N') ? m : k, an = (opa == 'N') ? k : m;
+        int64_t bm = (opb == 'N') ? k : n, bn = (opb == 'N') ? n : k;
+        auto Am = slate::Matrix<T>::fromLAPACK(am, an, A, lda, nb, 1, 1, MPI_COMM_WORLD);
+        auto Bm = slate::Matrix<T>::fromLAPACK(bm, bn, B, ldb, nb, 1, 1, MPI_COMM_WORLD);
+        auto Cm = slate::Matrix<T>::fromLAPACK(m, n, C, ldc, nb, 1, 1, MPI_COMM_WORLD);
+        auto opA = apply_op(Am, opa);
+        auto opB = apply_op(Bm, opb);
+        slate::Options opts = host_opts(la);
+        opts[Option::MethodGemm] = slate::MethodGemm::GemmA;
+        slate::gemm(scalar_of<T>(alpha), opA, opB, scalar_of<T>(beta), Cm, opts);
+        return 0;
+    });
+}
+
+// slate::getrf_nopiv (src/getrf_nopiv.cc); returns info
+template <typename T>
+int64_t ref_getrf_nopiv(int64_t m, int64_t n, int64_t nb, T* A, int64_t lda, int la)
+{
+    return guarded("ref_getrf_nopiv", [&]() -> int64_t {
+        auto Am = slate::Matrix<T>::fromLAPACK(m, n, A, lda, nb, 1, 1, MPI_COMM_WORLD);
+        return slate::getrf_nopiv(Am, host_opts(la));
+    });
+}
+
 }  // namespace
 
 extern "C" {
@@ -265,6 +407,61 @@ void ref_matgen_z(int dist, int64_t seed, int64_t m, int64_t n, int64_t ioff, in
 {
     slate::random::generate<zdouble>(slate::random::Dist(dist), seed, m, n, ioff, joff,
                                      (zdouble*)A, lda);
+}
+
+// ---- widened drivers: dtype 0 = double, 1 = complex<double>; scalars as 2 doubles ----
+#define BY_TYPE(call_d, call_z) (dtype == 1 ? (call_z) : (call_d))
+
+int64_t ref_rank_k_any(int dtype, int kind, int uplo, int opa, int64_t n, int64_t k, int64_t nb,
+                       const double* alpha, void* A, int64_t lda, const double* beta, void* C,
+                       int64_t ldc, int la)
+{
+    return BY_TYPE(ref_rank_k<double>(kind, uplo, opa, n, k, nb, alpha, (double*)A, lda, beta, (double*)C, ldc, la),
+                   ref_rank_k<zdouble>(kind, uplo, opa, n, k, nb, alpha, (zdouble*)A, lda, beta, (zdouble*)C, ldc, la));
+}
+
+int64_t ref_rank_2k_any(int dtype, int kind, int uplo, int opa, int64_t n, int64_t k, int64_t nb,
+                        const double* alpha, void* A, int64_t lda, void* B, int64_t ldb,
+                        const double* beta, void* C, int64_t ldc, int la)
+{
+    return BY_TYPE(ref_rank_2k<double>(kind, uplo, opa, n, k, nb, alpha, (double*)A, lda, (double*)B, ldb, beta, (double*)C, ldc, la),
+                   ref_rank_2k<zdouble>(kind, uplo, opa, n, k, nb, alpha, (zdouble*)A, lda, (zdouble*)B, ldb, beta, (zdouble*)C, ldc, la));
+}
+
+int64_t ref_hemm_any(int dtype, int kind, int side, int uplo, int64_t m, int64_t n, int64_t nb,
+                     const double* alpha, void* A, int64_t lda, void* B, int64_t ldb,
+                     const double* beta, void* C, int64_t ldc, int la)
+{
+    return BY_TYPE(ref_hemm<double>(kind, side, uplo, m, n, nb, alpha, (double*)A, lda, (double*)B, ldb, beta, (double*)C, ldc, la),
+                   ref_hemm<zdouble>(kind, side, uplo, m, n, nb, alpha, (zdouble*)A, lda, (zdouble*)B, ldb, beta, (zdouble*)C, ldc, la));
+}
+
+int64_t ref_trsm_any(int dtype, int side, int uplo, int opa, int diag, int64_t m, int64_t n, int64_t nb,
+                     const double* alpha, void* A, int64_t lda, void* B, int64_t ldb, int la)
+{
+    return BY_TYPE(ref_trsm<double>(side, uplo, opa, diag, m, n, nb, alpha, (double*)A, lda, (double*)B, ldb, la),
+                   ref_trsm<zdouble>(side, uplo, opa, diag, m, n, nb, alpha, (zdouble*)A, lda, (zdouble*)B, ldb, la));
+}
+
+int64_t ref_posv_any(int dtype, int uplo, int64_t n, int64_t nrhs, int64_t nb, void* A, int64_t lda,
+                     void* B, int64_t ldb, int la)
+{
+    return BY_TYPE(ref_posv<double>(uplo, n, nrhs, nb, (double*)A, lda, (double*)B, ldb, la),
+                   ref_posv<zdouble>(uplo, n, nrhs, nb, (zdouble*)A, lda, (zdouble*)B, ldb, la));
+}
+
+int64_t ref_gemmA_any(int dtype, int opa, int opb, int64_t m, int64_t n, int64_t k, int64_t nb,
+                      const double* alpha, void* A, int64_t lda, void* B, int64_t ldb,
+                      const double* beta, void* C, int64_t ldc, int la)
+{
+    return BY_TYPE(ref_gemmA<double>(opa, opb, m, n, k, nb, alpha, (double*)A, lda, (double*)B, ldb, beta, (double*)C, ldc, la),
+                   ref_gemmA<zdouble>(opa, opb, m, n, k, nb, alpha, (zdouble*)A, lda, (zdouble*)B, ldb, beta, (zdouble*)C, ldc, la));
+}
+
+int64_t ref_getrf_nopiv_any(int dtype, int64_t m, int64_t n, int64_t nb, void* A, int64_t lda, int la)
+{
+    return BY_TYPE(ref_getrf_nopiv<double>(m, n, nb, (double*)A, lda, la),
+                   ref_getrf_nopiv<zdouble>(m, n, nb, (zdouble*)A, lda, la));
 }
 
 }  // extern "C"

@@ -84,6 +84,19 @@ def ref():
         for f in (L.ref_internal_dpotrf, L.ref_internal_zpotrf):
             f.argtypes = [C.c_int, i64, dp, i64]
             f.restype = i64
+        # widened drivers: dtype 0 / 1, scalars as pointers to 2 doubles
+        ci, vp = C.c_int, C.c_void_p
+        if hasattr(L, "ref_rank_k_any"):
+            L.ref_rank_k_any.argtypes = [ci, ci, ci, ci, i64, i64, i64, dp, vp, i64, dp, vp, i64, ci]
+            L.ref_rank_2k_any.argtypes = [ci, ci, ci, ci, i64, i64, i64, dp, vp, i64, vp, i64, dp, vp, i64, ci]
+            L.ref_hemm_any.argtypes = [ci, ci, ci, ci, i64, i64, i64, dp, vp, i64, vp, i64, dp, vp, i64, ci]
+            L.ref_trsm_any.argtypes = [ci, ci, ci, ci, ci, i64, i64, i64, dp, vp, i64, vp, i64, ci]
+            L.ref_posv_any.argtypes = [ci, ci, i64, i64, i64, vp, i64, vp, i64, ci]
+            L.ref_gemmA_any.argtypes = [ci, ci, ci, i64, i64, i64, i64, dp, vp, i64, vp, i64, dp, vp, i64, ci]
+            L.ref_getrf_nopiv_any.argtypes = [ci, i64, i64, i64, vp, i64, ci]
+            for f in (L.ref_rank_k_any, L.ref_rank_2k_any, L.ref_hemm_any, L.ref_trsm_any,
+                      L.ref_posv_any, L.ref_gemmA_any, L.ref_getrf_nopiv_any):
+                f.restype = i64
         L.ref_matgen_d.argtypes = [C.c_int, i64, i64, i64, i64, i64, dp, i64]
         L.ref_matgen_z.argtypes = L.ref_matgen_d.argtypes
         L.ref_matgen_d.restype = None
