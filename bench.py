@@ -355,7 +355,9 @@ def main():
                  "lookahead": args.lookahead, "info": int(info), "ms": ms_p,
                  "value": pf / (ms_p * 1e-3) * 1e-12, "unit": "TFLOP/s",
                  "frac_of_fp64_tensor_peak": pf / (ms_p * 1e-3) * 1e-12 / (peak_tf * world),
-                 "gpu_launches": int(lp)}
+                 "gpu_launches": int(lp),
+                 # scheduling of the trailing update during potrf
+                 "update_blocks_per_cta_cap": int(os.environ.get("TE_ITEMS_PER_CTA", 0)) or (4 if world > 1 else 16)}
         # north-star check at full size: ||A - L L^H||_F / (n ||A||_F) <= 50 eps, evaluated with
         # the engine's own update kernels on a regenerated A (n^3/3 flops, outside the timing)
         free_b, total_b = C.c_size_t(), C.c_size_t()

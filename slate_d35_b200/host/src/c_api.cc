@@ -549,6 +549,18 @@ int sb_tile_layout_convert(void* A, int64_t i, int64_t j, int layout)
     });
 }
 
+/// owner of tile (i, j) on a p x q grid with ranks laid out column-major ('C') or row-major
+/// ('R') over the grid (include/slate/func.hh:100-118, process_2d_grid)
+int sb_grid_tile_rank(int order, int p, int q, int64_t i, int64_t j)
+{
+    int out = -1;
+    guarded([&] {
+        auto f = func::process_2d_grid(order == 'R' ? GridOrder::Row : GridOrder::Col, p, q);
+        out = f(ij_tuple{i, j});
+    });
+    return out;
+}
+
 int sb_tile_rank(void* A, int64_t i, int64_t j)
 {
     Handle* h = (Handle*)A;

@@ -49,7 +49,7 @@ def test_host_mirror_loads_and_refuses_cpu_targets():
 def test_product_never_links_the_oracle():
     """the shipped libraries must not depend on oracle/ (checked on the ELF NEEDED list)."""
     import subprocess
-    for so in ("libtile_engine.so", "libslate_b200.so"):
+    for so in ("libtile_engine.so", "libslate_b200.so", "libslate_b200_scalapack.so"):
         out = subprocess.run(["readelf", "-d", os.path.join(ROOT, "slate_d35_b200", "lib", so)],
                              capture_output=True, text=True).stdout
         assert "oracle" not in out and "slate_ref" not in out
@@ -96,3 +96,16 @@ def test_scalapack_argument_errors_need_no_gpu():
     # 15 full blocks of 64 over 3 processes, the 40 left over follow the last full block
     assert [sc.numroc(1000, 64, r, 3) for r in range(3)] == [360, 320, 320]
     assert [sc.numroc(1100, 64, r, 3) for r in range(3)] == [384, 384, 332]
+
+
+def test_process_grid_orders():
+    """func::process_2d_grid (include/slate/func.hh:100-118): BLACS column-major and row-major
+    rank layouts, as slate_scalapack_grid_set / fromScaLAPACK use them."""
+    from slate_d35_b200 import host
+    H = host.hostlib()
+    H.sb_grid_tile_rank.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64]
+    for p, q in ((1, 1), (2, 4), (4, 2), (3, 5)):
+        for i in range(9):
+            for j in range(11):
+                assert H.sb_grid_tile_rank(ord("C"), p, q, i, j) == (i % p) + (j % q) * p
+                assert H.sb_grid_tile_rank(ord("R"), p, q, i, j) == (i % p) * q + (j % q)
