@@ -13,7 +13,11 @@ GRIDS = [(2, 2), (2, 4), (4, 2), (1, 4)]
 
 @pytest.fixture(scope="module")
 def sl():
-    from slate_d35_b200 import host
+    from slate_d35_b200 import host, lib
+    if lib().te_device_count() > 0:
+        # with a GPU present a multi-rank initialize() wants a NCCL id; this test is about the
+        # host-side planning only and runs where the "not gpu" suite runs
+        pytest.skip("host-only planning test")
     return host
 
 
