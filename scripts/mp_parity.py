@@ -166,8 +166,10 @@ def main():
                 M.free()
 
     # hemm / symm, her2k and getrf_nopiv on the grids (their broadcast plans run over gloo in
-    # tests/mp_worker.py; this is the same on GPUs over NCCL)
-    for (p, q) in GRIDS[world]:
+    # tests/mp_worker.py and are replayed on 2x2 / 2x4 in tests/test_plans_grid.py; this is the
+    # same on GPUs over NCCL).  Written after the round's multi-GPU budget was spent, so NOT YET
+    # RUN on several GPUs: opt in with MP_PARITY_EXTRA=1 until it has been.
+    for (p, q) in (GRIDS[world] if os.environ.get("MP_PARITY_EXTRA") == "1" else []):
         n, nrhs, nb = 1500, 700, 256
         S0 = ol.matgen(30, n, n)
         S0 = (S0 + S0.T) / 2
