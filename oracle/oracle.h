@@ -79,6 +79,29 @@ void oracle_zgemm(int opa, int opb, int64_t m, int64_t n, int64_t k, int64_t nb,
 int64_t oracle_dpotrf(int uplo, int64_t n, int64_t nb, double* A, int64_t lda);
 int64_t oracle_zpotrf(int uplo, int64_t n, int64_t nb, double* A, int64_t lda);
 
+/* SURVEY.md section 8f.  src/her2k.cc:25-190 / src/syr2k.cc (conjugate = 1 / 0): rank-2k
+ * update of the uplo triangle by block columns of nb.  For her2k beta must be real. */
+void oracle_drank2k(int conjugate, int uplo, int opa, int64_t n, int64_t k, int64_t nb, double alpha,
+                    const double* A, int64_t lda, const double* B, int64_t ldb, double beta, double* C,
+                    int64_t ldc);
+void oracle_zrank2k(int conjugate, int uplo, int opa, int64_t n, int64_t k, int64_t nb,
+                    const double* alpha, const double* A, int64_t lda, const double* B, int64_t ldb,
+                    const double* beta, double* C, int64_t ldc);
+
+/* src/hemmC.cc:28-420 / src/symm.cc (herm = 1 / 0): C = alpha A B + beta C (side L) or
+ * alpha B A + beta C (side R); only the uplo triangle of A is read. */
+void oracle_dhemm(int herm, int side, int uplo, int64_t m, int64_t n, int64_t nb, double alpha,
+                  const double* A, int64_t lda, const double* B, int64_t ldb, double beta, double* C,
+                  int64_t ldc);
+void oracle_zhemm(int herm, int side, int uplo, int64_t m, int64_t n, int64_t nb, const double* alpha,
+                  const double* A, int64_t lda, const double* B, int64_t ldb, const double* beta,
+                  double* C, int64_t ldc);
+
+/* src/getrf_nopiv.cc:26-260 with src/internal/Tile_getrf_nopiv.hh on the diagonal tiles:
+ * A = L U in place, no pivoting; returns info (first exactly zero pivot, 1-based) */
+int64_t oracle_dgetrf_nopiv(int64_t m, int64_t n, int64_t nb, double* A, int64_t lda);
+int64_t oracle_zgetrf_nopiv(int64_t m, int64_t n, int64_t nb, double* A, int64_t lda);
+
 int oracle_num_threads(void);
 
 #ifdef __cplusplus

@@ -87,3 +87,32 @@ int64_t oracle_dpotrf(int uplo, int64_t n, int64_t nb, double* A, int64_t lda)
 
 int64_t oracle_zpotrf(int uplo, int64_t n, int64_t nb, double* A, int64_t lda)
 { return z_potrf_tiled(uplo, n, nb, (zc*)A, lda); }
+
+/* ---- SURVEY.md section 8f ---------------------------------------------------------------- */
+void oracle_drank2k(int conjugate, int uplo, int opa, int64_t n, int64_t k, int64_t nb, double alpha,
+                    const double* A, int64_t lda, const double* B, int64_t ldb, double beta, double* C,
+                    int64_t ldc)
+{ d_rank2k_tiled(conjugate, uplo, opa, n, k, nb, alpha, A, lda, B, ldb, beta, C, ldc); }
+
+void oracle_zrank2k(int conjugate, int uplo, int opa, int64_t n, int64_t k, int64_t nb,
+                    const double* alpha, const double* A, int64_t lda, const double* B, int64_t ldb,
+                    const double* beta, double* C, int64_t ldc)
+{ z_rank2k_tiled(conjugate, uplo, opa, n, k, nb, mkz(alpha), (const zc*)A, lda, (const zc*)B, ldb,
+                 mkz(beta), (zc*)C, ldc); }
+
+void oracle_dhemm(int herm, int side, int uplo, int64_t m, int64_t n, int64_t nb, double alpha,
+                  const double* A, int64_t lda, const double* B, int64_t ldb, double beta, double* C,
+                  int64_t ldc)
+{ d_hemm_tiled(herm, side, uplo, m, n, nb, alpha, A, lda, B, ldb, beta, C, ldc); }
+
+void oracle_zhemm(int herm, int side, int uplo, int64_t m, int64_t n, int64_t nb, const double* alpha,
+                  const double* A, int64_t lda, const double* B, int64_t ldb, const double* beta,
+                  double* C, int64_t ldc)
+{ z_hemm_tiled(herm, side, uplo, m, n, nb, mkz(alpha), (const zc*)A, lda, (const zc*)B, ldb,
+               mkz(beta), (zc*)C, ldc); }
+
+int64_t oracle_dgetrf_nopiv(int64_t m, int64_t n, int64_t nb, double* A, int64_t lda)
+{ return d_getrf_nopiv_tiled(m, n, nb, A, lda); }
+
+int64_t oracle_zgetrf_nopiv(int64_t m, int64_t n, int64_t nb, double* A, int64_t lda)
+{ return z_getrf_nopiv_tiled(m, n, nb, (zc*)A, lda); }

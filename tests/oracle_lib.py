@@ -50,6 +50,16 @@ def oracle():
         for f in (L.oracle_dpotrf, L.oracle_zpotrf):
             f.argtypes = [C.c_int, i64, i64, dp, i64]
             f.restype = i64
+        ci = C.c_int
+        L.oracle_drank2k.argtypes = [ci, ci, ci, i64, i64, i64, C.c_double, dp, i64, dp, i64, C.c_double, dp, i64]
+        L.oracle_zrank2k.argtypes = [ci, ci, ci, i64, i64, i64, dp, dp, i64, dp, i64, dp, dp, i64]
+        L.oracle_dhemm.argtypes = [ci, ci, ci, i64, i64, i64, C.c_double, dp, i64, dp, i64, C.c_double, dp, i64]
+        L.oracle_zhemm.argtypes = [ci, ci, ci, i64, i64, i64, dp, dp, i64, dp, i64, dp, dp, i64]
+        for f in (L.oracle_drank2k, L.oracle_zrank2k, L.oracle_dhemm, L.oracle_zhemm):
+            f.restype = None
+        for f in (L.oracle_dgetrf_nopiv, L.oracle_zgetrf_nopiv):
+            f.argtypes = [i64, i64, i64, dp, i64]
+            f.restype = i64
         for f in (L.oracle_matgen_d, L.oracle_matgen_z, L.oracle_tile_dgemm, L.oracle_tile_zgemm,
                   L.oracle_tile_dsyrk, L.oracle_tile_zherk, L.oracle_tile_dtrsm, L.oracle_tile_ztrsm,
                   L.oracle_dgemm, L.oracle_zgemm):

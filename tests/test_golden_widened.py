@@ -75,6 +75,42 @@ def test_reference_output_matches_numpy(name, spec):
     check_against(spec, x, GOLD[name], True)
 
 
+ORACLE_KINDS = ("her2k", "syr2k", "hemm", "symm", "getrf_nopiv")
+
+
+@pytest.mark.parametrize("name,spec", [c for c in CASES if c[1]["kind"] in ORACLE_KINDS],
+                         ids=[n for n, s in CASES if s["kind"] in ORACLE_KINDS])
+def test_c_oracle_matches_reference_output(name, spec):
+    """the plain-C restatements of the widened drivers (oracle/oracle_tiles_body.inc) against
+    what the unmodified reference returned for the same inputs"""
+    O = ol.oracle()
+    x = wc.inputs(spec, lambda seed, m, n, dt: ol.matgen(seed, m, n, dt))
+    pre, k, nb = spec["pre"], spec["kind"], wc.NB
+    a, b = wc.ALPHA[pre], wc.BETA[pre]
+    z = pre == "z"
+    sc = (lambda v: ol.Z(v)) if z else (lambda v: float(np.real(v)))
+    y = {n_: np.asfortranarray(v.copy()) for n_, v in x.items()}
+    gold = GOLD[name]
+    if k in ("her2k", "syr2k"):
+        f = O.oracle_zrank2k if z else O.oracle_drank2k
+        beta = b.real if k == "her2k" else b
+        f(1 if k == "her2k" else 0, ord(spec["uplo"]), ord(spec["opa"]), spec["n"], spec["k"], nb, sc(a),
+          ol.P(y["A"]), y["A"].shape[0], ol.P(y["B"]), y["B"].shape[0], sc(beta), ol.P(y["C"]), spec["n"])
+        tri = np.tril if spec["uplo"] == "L" else np.triu
+        assert np.abs(tri(y["C"]) - tri(gold)).max() <= 2 * tolerance(spec, np.abs(gold).max())
+        other = (lambda q: np.triu(q, 1)) if spec["uplo"] == "L" else (lambda q: np.tril(q, -1))
+        assert np.array_equal(other(y["C"]), other(gold))
+    elif k in ("hemm", "symm"):
+        f = O.oracle_zhemm if z else O.oracle_dhemm
+        f(1 if k == "hemm" else 0, ord(spec["side"]), ord(spec["uplo"]), spec["m"], spec["n"], nb, sc(a),
+          ol.P(y["A"]), y["A"].shape[0], ol.P(y["B"]), spec["m"], sc(b), ol.P(y["C"]), spec["m"])
+        assert np.abs(y["C"] - gold).max() <= 2 * tolerance(spec, np.abs(gold).max())
+    else:
+        f = O.oracle_zgetrf_nopiv if z else O.oracle_dgetrf_nopiv
+        assert f(spec["m"], spec["n"], nb, ol.P(y["A"]), spec["m"]) == 0
+        assert np.abs(y["A"] - gold).max() <= 200 * EPS * np.abs(gold).max()
+
+
 # ------------------------------------------------------------------------------------------
 @pytest.fixture(scope="module")
 def sl():
