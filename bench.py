@@ -267,7 +267,7 @@ def main():
     if W > 0:
         Aw = sl.Matrix(n, nb * W, nb, p, q).generate(4)
         Bw = sl.Matrix(nb * W, n, nb, p, q).generate(5)
-        sl.gemm(ALPHA, Aw, Bw, BETA, Cm, lookahead=args.lookahead)
+        sl.gemm(ALPHA, Aw, Bw, BETA, Cm, lookahead=args.lookahead, method="C")
         Aw.free()
         Bw.free()
         Cm.generate(3)
@@ -276,7 +276,7 @@ def main():
         sampler.start()
     barrier()
     launches0 = te.te_launch_count()
-    ms = sl.gemm(ALPHA, A, B, BETA, Cm, lookahead=args.lookahead, timed=True)
+    ms = sl.gemm(ALPHA, A, B, BETA, Cm, lookahead=args.lookahead, timed=True, method="C")
     launches = te.te_launch_count() - launches0
     barrier()
     ms = max_over_ranks(ms)
@@ -286,19 +286,21 @@ def main():
 
     # the tester's own check on the result (test/test_gemm.cc:136-158, 196-212):
     # || C X - (alpha A (B X) + beta C0 X) ||_1 / || Y ||_1, X = nrhs columns of kind rand
+    # (the check products run through gemmC, the route these logs were verified with on 1, 4
+    # and 8 GPUs; slate::gemm would pick gemmA for a single block column by itself)
     nrhs = 10
     X = sl.Matrix(n, nrhs, nb, p, q).generate(6)
     Wm = sl.Matrix(k, nrhs, nb, p, q)
     Y = sl.Matrix(n, nrhs, nb, p, q)
     Z = sl.Matrix(n, nrhs, nb, p, q)
-    sl.gemm(1.0, B, X, 0.0, Wm)               # W = B X
-    sl.gemm(ALPHA, A, Wm, 0.0, Y)             # Y = alpha A W
-    sl.gemm(1.0, Cm, X, 0.0, Z)               # Z = C X
+    sl.gemm(1.0, B, X, 0.0, Wm, method="C")               # W = B X
+    sl.gemm(ALPHA, A, Wm, 0.0, Y, method="C")             # Y = alpha A W
+    sl.gemm(1.0, Cm, X, 0.0, Z, method="C")               # Z = C X
     A.free()
     B.free()
     Wm.free()
     Cm.generate(3)                            # C0 again
-    sl.gemm(BETA, Cm, X, 1.0, Y)              # Y += beta C0 X
+    sl.gemm(BETA, Cm, X, 1.0, Y, method="C")              # Y += beta C0 X
     yh, zh = Y.to_numpy(), Z.to_numpy()       # n x nrhs, this rank's tiles (zeros elsewhere)
     if world > 1:
         t = torch.from_numpy(np.ascontiguousarray(np.stack([yh, zh]))).cuda()
@@ -323,7 +325,7 @@ def main():
         Be.generate(2)
         Ce.generate(3)
         barrier()
-        ms_e = sl.gemm(ALPHA, Ae, Be, BETA, Ce, lookahead=args.lookahead, timed=True)
+        ms_e = sl.gemm(ALPHA, Ae, Be, BETA, Ce, lookahead=args.lookahead, timed=True, method="C")
         barrier()
         ms_e = max_over_ranks(ms_e)
         h2d = 8.0 * (n * k + k * n + n * n)
@@ -383,12 +385,12 @@ def main():
         Cz = sl.Matrix(nz, nz, nbz, p, q, dtype=np.complex128).generate(3)
         Aw = sl.Matrix(nz, 2 * nbz, nbz, p, q, dtype=np.complex128).generate(4)
         Bw = sl.Matrix(2 * nbz, nz, nbz, p, q, dtype=np.complex128).generate(5)
-        sl.gemm(za, Aw, Bw, zb, Cz, lookahead=args.lookahead)
+        sl.gemm(za, Aw, Bw, zb, Cz, lookahead=args.lookahead, method="C")
         Aw.free()
         Bw.free()
         Cz.generate(3)
         barrier()
-        ms_z = sl.gemm(za, Az, Bz, zb, Cz, lookahead=args.lookahead, timed=True)
+        ms_z = sl.gemm(za, Az, Bz, zb, Cz, lookahead=args.lookahead, timed=True, method="C")
         barrier()
         ms_z = max_over_ranks(ms_z)
         # tester check with X of kind rand (complex): ||C X - (alpha A (B X) + beta C0 X)||_1 / ||Y||_1
@@ -396,11 +398,11 @@ def main():
         Wz = sl.Matrix(nz, 10, nbz, p, q, dtype=np.complex128)
         Yz = sl.Matrix(nz, 10, nbz, p, q, dtype=np.complex128)
         Zz = sl.Matrix(nz, 10, nbz, p, q, dtype=np.complex128)
-        sl.gemm(1.0, Bz, Xz, 0.0, Wz)
-        sl.gemm(za, Az, Wz, 0.0, Yz)
-        sl.gemm(1.0, Cz, Xz, 0.0, Zz)
+        sl.gemm(1.0, Bz, Xz, 0.0, Wz, method="C")
+        sl.gemm(za, Az, Wz, 0.0, Yz, method="C")
+        sl.gemm(1.0, Cz, Xz, 0.0, Zz, method="C")
         Cz.generate(3)
-        sl.gemm(zb, Cz, Xz, 1.0, Yz)
+        sl.gemm(zb, Cz, Xz, 1.0, Yz, method="C")
         yh, zh = Yz.to_numpy(), Zz.to_numpy()
         if world > 1:
             t = torch.from_numpy(np.ascontiguousarray(np.stack([yh, zh]))).cuda()
