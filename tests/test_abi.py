@@ -109,3 +109,24 @@ def test_process_grid_orders():
             for j in range(11):
                 assert H.sb_grid_tile_rank(ord("C"), p, q, i, j) == (i % p) + (j % q) * p
                 assert H.sb_grid_tile_rank(ord("R"), p, q, i, j) == (i % p) * q + (j % q)
+
+
+def test_scalapack_style_c_program_links_and_fails_loudly_without_gpu(tmp_path):
+    """examples/example_pdgemm_pdpotrf.c: a plain C caller of pdgemm_ / pdpotrf_ compiles against
+    include/slate_b200_scalapack.h (valid C, not only C++) and links against the three shared
+    libraries.  Without a GPU the calls report an error and leave the output alone -- there is
+    no CPU path to fall back to; with one the program factors its matrix."""
+    import subprocess
+    from slate_d35_b200 import lib
+    libdir = os.path.join(ROOT, "slate_d35_b200", "lib")
+    exe = str(tmp_path / "example_pd")
+    subprocess.check_call(["gcc", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "examples", "example_pdgemm_pdpotrf.c"), "-L" + libdir,
+                           "-lslate_b200_scalapack", "-lslate_b200", "-ltile_engine",
+                           "-Wl,-rpath," + libdir, "-lm", "-o", exe])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    if lib().te_device_count() == 0:
+        assert r.returncode != 0 and "status = 1" in r.stdout
+        assert "pdgemm" in r.stderr and "pdpotrf" in r.stderr
+    else:
+        assert r.returncode == 0 and "info = 0" in r.stdout and "status = 0" in r.stdout
