@@ -55,6 +55,7 @@ def hostlib():
     L.sb_plan_gemmA_step.argtypes = [vp, vp, vp, i64, ip, i64, ip]
     L.sb_plan_getrf_nopiv_step.argtypes = [vp, i64, ip, i64, ip]
     L.sb_plan_hemm_step.argtypes = [vp, vp, vp, i64, ip, i64, ip]
+    L.sb_plan_pairs.argtypes = [C.c_int, vp, vp, vp, i64, C.c_int, C.c_int, ip, i64, ip]
     L.sb_tile_rank.argtypes = [vp, i64, i64]
     L.sb_tile_layout.argtypes = [vp, i64, i64]
     L.sb_tile_layout_convert.argtypes = [vp, i64, i64, C.c_int]
@@ -351,6 +352,25 @@ def plan_gemmA_step(A, B, Cm, k):
     used = i64()
     _check(hostlib().sb_plan_gemmA_step(A.h, B.h, Cm.h, k, buf, cap, C.byref(used)))
     return _unflatten(buf, used.value)
+
+
+def plan_pairs(kind, mats, k, which, rank):
+    """Messages of one broadcast list grouped by (root, destination) pair as `rank` sees them
+    (BaseMatrix::bcastPairs): kind "gemm" (mats = (A, B, C)) or "potrf" (mats = (A,)).
+    Returns [(direction, peer, bytes, [(i, j), ...])], direction 0 = send, 1 = receive."""
+    cap = 1 << 16
+    buf = (i64 * cap)()
+    used = i64()
+    hs = [m.h for m in mats] + [None] * (3 - len(mats))
+    _check(hostlib().sb_plan_pairs(0 if kind == "gemm" else 1, hs[0], hs[1], hs[2], k, which, rank, buf,
+                                   cap, C.byref(used)))
+    out, pos = [], 0
+    while pos < used.value:
+        d, peer, nt, nbytes = (int(x) for x in buf[pos:pos + 4])
+        tiles = [(int(buf[pos + 4 + 2 * t]), int(buf[pos + 5 + 2 * t])) for t in range(nt)]
+        out.append((d, peer, nbytes, tiles))
+        pos += 4 + 2 * nt
+    return out
 
 
 def plan_hemm_step(A, B, Cm, k):

@@ -17,6 +17,7 @@
 
 #include <algorithm>
 #include <list>
+#include <map>
 #include <set>
 #include <vector>
 
@@ -454,6 +455,44 @@ public:
         return plan;
     }
 
+    /// All tiles one rank sends to (receives from) one peer within a list, in plan order.
+    struct PairMsg { int peer; std::vector<size_t> ops; size_t bytes; };
+
+    /// Groups a broadcast plan by (root, destination) pair as seen from rank `me`: the messages
+    /// `me` sends as a root and those it receives.  Sender and receiver derive the same message
+    /// (same tiles, same order, same byte count) from the same plan, so a whole pair can travel
+    /// as ONE NCCL message instead of one per tile (95 GB/s per pair at 2 MiB against 316 GB/s at
+    /// 128 MiB on this pool's NVLink, scripts/mp_commbench.py).  Pure index arithmetic.
+    void bcastPairs(std::vector<BcastOp> const& plan, int me, std::vector<PairMsg>* sends,
+                    std::vector<PairMsg>* recvs) const
+    {
+        std::map<int, size_t> send_at, recv_at;
+        for (size_t o = 0; o < plan.size(); ++o) {
+            auto const& op = plan[o];
+            const size_t bytes = sizeof(scalar_t) * (size_t)tileMb(op.i) * (size_t)tileNb(op.j);
+            if (op.root == me) {
+                for (int d : op.dests) {
+                    auto it = send_at.find(d);
+                    if (it == send_at.end()) {
+                        it = send_at.emplace(d, sends->size()).first;
+                        sends->push_back(PairMsg{d, {}, 0});
+                    }
+                    (*sends)[it->second].ops.push_back(o);
+                    (*sends)[it->second].bytes += bytes;
+                }
+            }
+            else if (std::find(op.dests.begin(), op.dests.end(), me) != op.dests.end()) {
+                auto it = recv_at.find(op.root);
+                if (it == recv_at.end()) {
+                    it = recv_at.emplace(op.root, recvs->size()).first;
+                    recvs->push_back(PairMsg{op.root, {}, 0});
+                }
+                (*recvs)[it->second].ops.push_back(o);
+                (*recvs)[it->second].bytes += bytes;
+            }
+        }
+    }
+
     /// One tile reduction of a plan: the partial sums of tile (i, j) held by `sources` are
     /// added into the instance on `root`.
     struct ReduceOp { int64_t i, j; int root; std::vector<int> sources; };
@@ -506,6 +545,7 @@ protected:
 
     void tileGet(int64_t i, int64_t j, int device, bool modify, int queue);
     void updateOrigin(int64_t i, int64_t j);
+    void bcastCoalesced(std::vector<BcastOp> const& plan);
     /// true if tile (i, j) has a valid device instance in the other layout
     bool needsConvert(int64_t i, int64_t j, LayoutConvert lc)
     {
@@ -658,6 +698,16 @@ void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
     }
 
     slate_assert(comm->nccl != nullptr);
+    // Opt-in: one message per (root, destination) pair instead of one per tile.  Written after
+    // the round's multi-GPU budget was spent: NOT YET RUN on GPUs, so off unless asked for.
+    static const bool coalesce = [] {
+        const char* e = std::getenv("SLATE_B200_BCAST_COALESCE");
+        return e && e[0] == '1';
+    }();
+    if (coalesce) {
+        bcastCoalesced(bcastPlan(bcast_list));
+        return;
+    }
     void* stream = eng.comm_stream();
     bool any = false;
     for (auto const& op : bcastPlan(bcast_list)) {
@@ -702,6 +752,125 @@ void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
         eng.mark_comm();
         device_copies_pending_ = false;
     }
+}
+
+//------------------------------------------------------------------------------
+/// listBcastMT with one NCCL message per (root, destination) pair (bcastPairs).  A root whose
+/// tiles for a destination are adjacent in memory sends them in place; otherwise it packs them
+/// into a staging slab (device-to-device copies on the comm stream).  A destination receives a
+/// multi-tile message into the slab and copies the tiles out into their workspace blocks.
+template <typename scalar_t>
+void BaseMatrix<scalar_t>::bcastCoalesced(std::vector<BcastOp> const& plan)
+{
+    Engine& eng = Engine::instance();
+    Comm* comm = storage_->comm_;
+    const int me = comm->rank;
+    void* stream = eng.comm_stream();
+    std::vector<PairMsg> sends, recvs;
+    bcastPairs(plan, me, &sends, &recvs);
+    if (sends.empty() && recvs.empty()) {
+        if (device_copies_pending_) { eng.mark_comm(); device_copies_pending_ = false; }
+        return;
+    }
+    auto tile_of = [&](size_t o) -> Tile<scalar_t>* {
+        return storage_->at(globalIndex(plan[o].i, plan[o].j)).dev;
+    };
+    auto align256 = [](size_t b) { return (b + 255) & ~(size_t)255; };
+
+    // roots: tiles valid on the device, in ColMajor, behind their producers
+    std::vector<char> prepared(plan.size(), 0);
+    for (auto const& m : sends)
+        for (size_t o : m.ops) {
+            if (prepared[o]) continue;
+            prepared[o] = 1;
+            const int64_t i = plan[o].i, j = plan[o].j;
+            tileGet(i, j, 0, false, -1);
+            auto& node = storage_->at(globalIndex(i, j));
+            if (node.dev->layout() != Layout::ColMajor) tileLayoutConvert(i, j, 0, Layout::ColMajor, -1);
+            eng.comm_wait_queue_seq(node.write_queue, node.write_seq);
+            slate_assert(node.dev->isContiguous());
+        }
+    // destinations: workspace tiles (tilePrepareToReceive)
+    for (auto const& m : recvs)
+        for (size_t o : m.ops) {
+            const ij_tuple gij = globalIndex(plan[o].i, plan[o].j);
+            auto* node = storage_->find(gij);
+            if (!node || !node->dev) storage_->tileInsert(gij, 0, TileKind::Workspace);
+            auto& nd = storage_->at(gij);
+            nd.receive_count += 1;
+            nd.dev_state = MOSI::Shared;
+            nd.write_queue = -1;
+            nd.comm_seq = eng.next_comm_seq();
+        }
+
+    // which messages need staging
+    auto adjacent = [&](PairMsg const& m) {
+        for (size_t t = 0; t + 1 < m.ops.size(); ++t) {
+            Tile<scalar_t>* a = tile_of(m.ops[t]);
+            if ((char*)a->data() + a->bytes() != (char*)tile_of(m.ops[t + 1])->data()) return false;
+        }
+        return true;
+    };
+    std::vector<char> send_staged(sends.size(), 0);
+    size_t need = 0;
+    for (size_t s = 0; s < sends.size(); ++s)
+        if (sends[s].ops.size() > 1 && !adjacent(sends[s])) {
+            send_staged[s] = 1;
+            need += align256(sends[s].bytes);
+        }
+    for (auto const& m : recvs)
+        if (m.ops.size() > 1) need += align256(m.bytes);
+    Engine::CommSlab* slab = need ? &eng.acquire_comm_slab(need) : nullptr;
+    char* cursor = slab ? (char*)slab->dev : nullptr;
+
+    // pack
+    std::vector<void*> send_ptr(sends.size()), recv_ptr(recvs.size());
+    for (size_t s = 0; s < sends.size(); ++s) {
+        if (!send_staged[s]) {
+            send_ptr[s] = tile_of(sends[s].ops[0])->data();
+            continue;
+        }
+        send_ptr[s] = cursor;
+        char* p = cursor;
+        for (size_t o : sends[s].ops) {
+            Tile<scalar_t>* t = tile_of(o);
+            slate_te_call(te_memcpy_async(p, t->data(), t->bytes(), TE_COPY_D2D, stream));
+            p += t->bytes();
+        }
+        cursor += align256(sends[s].bytes);
+    }
+    for (size_t r = 0; r < recvs.size(); ++r) {
+        if (recvs[r].ops.size() == 1) {
+            recv_ptr[r] = tile_of(recvs[r].ops[0])->data();
+            continue;
+        }
+        recv_ptr[r] = cursor;
+        cursor += align256(recvs[r].bytes);
+    }
+
+    // one NCCL group: one send / recv per peer
+    eng.trace_begin(-1, "bcast_coalesced", (int64_t)plan.size());
+    slate_te_call(te_comm_group_start());
+    for (size_t s = 0; s < sends.size(); ++s)
+        slate_te_call(te_comm_send(comm->nccl, send_ptr[s], sends[s].bytes, sends[s].peer, stream));
+    for (size_t r = 0; r < recvs.size(); ++r)
+        slate_te_call(te_comm_recv(comm->nccl, recv_ptr[r], recvs[r].bytes, recvs[r].peer, stream));
+    slate_te_call(te_comm_group_end());
+
+    // unpack
+    for (size_t r = 0; r < recvs.size(); ++r) {
+        if (recvs[r].ops.size() == 1) continue;
+        const char* p = (const char*)recv_ptr[r];
+        for (size_t o : recvs[r].ops) {
+            Tile<scalar_t>* t = tile_of(o);
+            slate_te_call(te_memcpy_async(t->data(), p, t->bytes(), TE_COPY_D2D, stream));
+            p += t->bytes();
+        }
+    }
+    eng.trace_end(-1);
+    if (slab) eng.retire_comm_slab(*slab);
+    eng.mark_comm();
+    device_copies_pending_ = false;
 }
 
 //------------------------------------------------------------------------------

@@ -133,6 +133,19 @@ public:
     /// Call after the kernel that reads the slot was launched on queue q.
     void retire_desc(int q, DescSlot& slot);
 
+    // ---- staging slabs of the comm stream (coalesced broadcasts, SLATE_B200_BCAST_COALESCE) ----
+    struct CommSlab {
+        void* dev = nullptr;
+        size_t capacity = 0;
+        void* event = nullptr;
+        bool pending = false;
+    };
+    /// A device buffer of at least `bytes` for pack / unpack copies on the comm stream; blocks
+    /// only if all slabs of the ring still belong to unfinished broadcasts.
+    CommSlab& acquire_comm_slab(size_t bytes);
+    /// Call after the last comm-stream operation that touches the slab was enqueued.
+    void retire_comm_slab(CommSlab& slab);
+
     /// Device scratch private to queue q (grows; stream-ordered reuse on that queue).
     void* scratch(int q, size_t bytes);
     /// One device int per (queue, slot) for potrf's info.
@@ -191,6 +204,9 @@ private:
     void* scratch_[MaxQueues] = {};
     size_t scratch_bytes_[MaxQueues] = {};
     int* info_base_ = nullptr;
+    static const int CommSlabs = 4;
+    CommSlab comm_slab_[CommSlabs];
+    int comm_slab_next_ = 0;
     std::deque<Deferred> deferred_;
     std::vector<void*> event_pool_;
     std::recursive_mutex mu_;

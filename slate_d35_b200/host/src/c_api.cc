@@ -561,6 +561,45 @@ int sb_grid_tile_rank(int order, int p, int q, int64_t i, int64_t j)
     return out;
 }
 
+/// The (root, destination) messages of one broadcast list as rank `rank` sees them
+/// (BaseMatrix::bcastPairs; SLATE_B200_BCAST_COALESCE): kind 0 = list `which` of gemm step k
+/// (A, B, C given), kind 1 = list `which` of potrf step k (A given).  Records
+/// [direction (0 send, 1 receive), peer, ntiles, bytes, i0, j0, i1, j1, ...].
+int sb_plan_pairs(int kind, void* A, void* B, void* C, int64_t k, int which, int rank, int64_t* out,
+                  int64_t cap, int64_t* used)
+{
+    Handle *ha = (Handle*)A, *hb = (Handle*)B, *hc = (Handle*)C;
+    return guarded([&] {
+        typedef BaseMatrix<double> Base;
+        std::vector<Base::BcastOp> plan;
+        std::vector<Base::PairMsg> sends, recvs;
+        Base* M = nullptr;
+        if (kind == 0) {
+            auto& a = as_general<double>(ha);  auto& b = as_general<double>(hb);
+            auto& c = as_general<double>(hc);
+            auto list = gemm_bcast_list(which, a, b, c, k);
+            M = (which == 0) ? (Base*)&a : (Base*)&b;
+            plan = M->bcastPlan(list);
+        }
+        else {
+            auto& a = as_herm<double>(ha);
+            auto list = potrf_bcast_list(which, a, k);
+            M = &a;
+            plan = M->bcastPlan(list);
+        }
+        M->bcastPairs(plan, rank, &sends, &recvs);
+        int64_t pos = 0;
+        for (int dir = 0; dir < 2; ++dir)
+            for (auto const& m : (dir == 0 ? sends : recvs)) {
+                if (pos + 4 + 2 * (int64_t)m.ops.size() > cap) slate_error("plan buffer too small");
+                out[pos++] = dir;  out[pos++] = m.peer;  out[pos++] = (int64_t)m.ops.size();
+                out[pos++] = (int64_t)m.bytes;
+                for (size_t o : m.ops) { out[pos++] = plan[o].i;  out[pos++] = plan[o].j; }
+            }
+        *used = pos;
+    });
+}
+
 int sb_tile_rank(void* A, int64_t i, int64_t j)
 {
     Handle* h = (Handle*)A;

@@ -279,6 +279,32 @@ Engine::DescSlot& Engine::acquire_desc(int q, size_t bytes)
     return s;
 }
 
+Engine::CommSlab& Engine::acquire_comm_slab(size_t bytes)
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    CommSlab& s = comm_slab_[comm_slab_next_];
+    comm_slab_next_ = (comm_slab_next_ + 1) % CommSlabs;
+    if (s.pending) {
+        slate_te_call(te_event_sync(s.event));
+        s.pending = false;
+    }
+    if (s.capacity < bytes) {
+        if (s.dev) slate_te_call(te_device_free(device_, s.dev));
+        size_t cap = bytes + bytes / 4;
+        cap = (cap + ((size_t)1 << 20) - 1) & ~(((size_t)1 << 20) - 1);
+        slate_te_call(te_device_malloc(device_, cap, &s.dev));
+        s.capacity = cap;
+    }
+    if (!s.event) slate_te_call(te_event_create(device_, 0, &s.event));
+    return s;
+}
+
+void Engine::retire_comm_slab(CommSlab& s)
+{
+    slate_te_call(te_event_record(s.event, comm_stream()));
+    s.pending = true;
+}
+
 void Engine::upload_desc(int q, DescSlot& s, size_t bytes)
 {
     // By kernel while bulk host<->device tile traffic is in flight (a descriptor copy would

@@ -136,3 +136,52 @@ def test_potrf_hemm_getrf_plans(sl, p, q):
                 r = owner(G, sl, i, j)
                 assert (i, k) in have[r] and (k, j) in have[r]
     sl.finalize()
+
+
+@pytest.mark.parametrize("p,q", GRIDS)
+def test_pair_messages_match_on_both_sides(sl, p, q):
+    """BaseMatrix::bcastPairs (one message per root / destination pair, the opt-in coalesced
+    broadcast): what r sends to d is exactly what d expects from r -- same tiles, same order,
+    same byte count -- and together the messages are the plan, nothing more."""
+    world = p * q
+    sl.initialize(0, 0, world, None)
+    nb, nt = 8, 9
+    n = nt * nb - 3
+    H = sl.HermitianMatrix("L", n, nb, p, q, origin="N")
+    A = sl.Matrix(n, n, nb, p, q, origin="N")
+    B = sl.Matrix(n, n, nb, p, q, origin="N")
+    Cm = sl.Matrix(n, n, nb, p, q, origin="N")
+
+    def check(kind, mats, k, which, plan_ops):
+        msgs = [sl.plan_pairs(kind, mats, k, which, r) for r in range(world)]
+        sent = {}
+        for r in range(world):
+            peers = [m[1] for m in msgs[r] if m[0] == 0]
+            assert len(peers) == len(set(peers)) and r not in peers      # one message per peer
+            for d_, peer, nbytes, tiles in msgs[r]:
+                if d_ == 0:
+                    sent[(r, peer)] = (nbytes, tiles)
+        got = {}
+        for d in range(world):
+            for d_, peer, nbytes, tiles in msgs[d]:
+                if d_ == 1:
+                    got[(peer, d)] = (nbytes, tiles)
+        assert sent == got
+        want = {}
+        for w, i, j, root, dests in plan_ops:
+            if w == which:
+                for d in dests:
+                    want.setdefault((root, d), []).append((i, j))
+        assert {key: v[1] for key, v in sent.items()} == want
+        for (r, d), (nbytes, tiles) in sent.items():
+            rows = lambda i: min(nb, n - i * nb)
+            assert nbytes == 8 * sum(rows(i) * rows(j) for i, j in tiles)
+
+    for k in (0, 3, nt - 2):
+        ops = sl.plan_potrf_step(H, k)
+        check("potrf", (H,), k, 0, ops)
+        check("potrf", (H,), k, 1, ops)
+        ops = sl.plan_gemm_step(A, B, Cm, k)
+        check("gemm", (A, B, Cm), k, 0, ops)
+        check("gemm", (A, B, Cm), k, 1, ops)
+    sl.finalize()
