@@ -57,11 +57,15 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--potrf-n", type=int, default=N_POTRF)
     ap.add_argument("--lookahead", type=int, default=1)
-    ap.add_argument("--zgemm", action="store_true",
-                    help="also run config 5: slate::gemm complex<double> n=32768 nb=384 (ragged tiles)")
+    ap.add_argument("--zgemm", action="store_true", help="(default now; kept for old command lines)")
+    ap.add_argument("--no-zgemm", action="store_true",
+                    help="skip config 5: slate::gemm complex<double> n=32768 nb=384 (ragged tiles)")
     ap.add_argument("--zgemm-n", type=int, default=32768)
-    ap.add_argument("--herk", action="store_true",
-                    help="also run config 4: one internal::herk / syrk tile update, k = nb = 512")
+    ap.add_argument("--herk", action="store_true", help="(default now; kept for old command lines)")
+    ap.add_argument("--no-herk", action="store_true",
+                    help="skip config 4: one internal::herk / syrk tile update, k = nb = 512 (1 GPU)")
+    ap.add_argument("--no-parity", action="store_true",
+                    help="skip the small multi-rank parity block against the CPU reference (N > 1)")
     ap.add_argument("--herk-n", type=int, default=32768)
     return ap.parse_args()
 
@@ -123,13 +127,28 @@ class ClockSampler:
         return out
 
 
+def host_cores():
+    """cores this process may run on (torchrun exports OMP_NUM_THREADS=1: not a core count)"""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def reference_lib():
-    """(ctypes lib, kind): oracle/_ref when built, else the oracle port."""
+    """(ctypes lib, kind): oracle/_ref when built, else the oracle port; its OpenMP team is
+    set to every host core explicitly, whatever OMP_NUM_THREADS the launcher exported."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as ol
     if ol.have_ref():
-        return ol, ol.ref(), "reference"
-    return ol, ol.oracle(), "port"
+        L, kind = ol.ref(), "reference"
+        if hasattr(L, "ref_set_num_threads"):
+            L.ref_set_num_threads(host_cores())
+    else:
+        L, kind = ol.oracle(), "port"
+        if hasattr(L, "oracle_set_num_threads"):
+            L.oracle_set_num_threads(host_cores())
+    return ol, L, kind
 
 
 def time_reference_gemm(n, k, nb, reps):
@@ -156,7 +175,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    os.environ.setdefault("OMP_NUM_THREADS", str(os.cpu_count()))
+    os.environ["OMP_NUM_THREADS"] = str(host_cores())      # override torchrun's OMP_NUM_THREADS=1
     # each step = one block outer product (k = 512) of a bounded m = n sample
     n_s = 16384 if args.n == N_GEMM else min(args.n, 16384)
     k = NB * args.steps
@@ -176,6 +195,110 @@ def run_reference(args):
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------
+def multirank_parity(sl, world, rank, p, q, lookahead):
+    """Small ragged problems on this job's p x q grid, compared on rank 0 with the reference's
+    own Target::HostTask results (oracle/_ref; the oracle port if that is not built) on the same
+    matgen inputs.  The CPU side is the CHECKER, outside every timed region.  Errors in units of
+    eps = 2^-52; bounds: the reference's 3 sqrt(k) eps for a block update
+    (unit_test/test_internal_blas.cc:446-447), 50 eps for factors, solutions and backward errors
+    (north star), 25 eps for the tester's solve residual (test/test_posv.cc:302-343)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    eps = 2.0 ** -52
+
+    def assemble(M):
+        a = M.to_numpy()
+        if world > 1:
+            t = torch.from_numpy(np.ascontiguousarray(a)).cuda()
+            dist.all_reduce(t)
+            a = t.cpu().numpy()
+        return np.asfortranarray(a)
+
+    ol = L = kind = None
+    if rank == 0:
+        ol, L, kind = reference_lib()
+    out = {"checker": None, "grid": f"{p}x{q}", "cases": {}}
+    worst = 0.0
+    ok_all = True
+
+    def record(name, err, bound):
+        nonlocal worst, ok_all
+        out["cases"][name] = {"err_eps": err / eps, "bound_eps": bound / eps}
+        worst = max(worst, err / eps)
+        ok_all = ok_all and (err <= bound)
+
+    # ---- gemm: ragged in every dimension, tester alpha / beta ----
+    m, n, k, nb = 2000, 1900, 1100, 256
+    A = sl.Matrix(m, k, nb, p, q).generate(1)
+    B = sl.Matrix(k, n, nb, p, q).generate(2)
+    Cm = sl.Matrix(m, n, nb, p, q).generate(3)
+    sl.gemm(ALPHA, A, B, BETA, Cm, lookahead=lookahead, method="C")
+    got = assemble(Cm)
+    for M in (A, B, Cm):
+        M.free()
+    if rank == 0:
+        A0, B0, want = ol.matgen(1, m, k), ol.matgen(2, k, n), ol.matgen(3, m, n)
+        if kind == "reference":
+            L.ref_dgemm(ord("N"), ord("N"), m, n, k, nb, ALPHA, ol.P(A0), m, ol.P(B0), k, BETA, ol.P(want), m, 1)
+        else:
+            L.oracle_dgemm(ord("N"), ord("N"), m, n, k, nb, ALPHA, ol.P(A0), m, ol.P(B0), k, BETA, ol.P(want), m)
+        record("gemm m=2000 n=1900 k=1100 nb=256", float(np.abs(got - want).max() / np.abs(want).max()),
+               3 * k ** 0.5 * eps)
+
+    # ---- potrf, both triangles: factor against the reference's, and the backward error ----
+    n, nb = 2000, 256
+    for uplo in "LU":
+        H = sl.HermitianMatrix(uplo, n, nb, p, q).generate(7, dominant=True)
+        info = sl.potrf(H, lookahead=lookahead)
+        got = assemble(H)
+        H.free()
+        if rank == 0:
+            A0 = ol.matgen(7, n, n)
+            A0[np.arange(n), np.arange(n)] += n
+            want = A0.copy(order="F")
+            fn = L.ref_dpotrf if kind == "reference" else L.oracle_dpotrf
+            args = (ord(uplo), n, nb, ol.P(want), n) + ((1,) if kind == "reference" else ())
+            info_ref = fn(*args)
+            tri = np.tril if uplo == "L" else np.triu
+            F = tri(got)
+            S = tri(A0) + tri(A0, -1 if uplo == "L" else 1).T          # the matrix potrf sees
+            R = (F @ F.T if uplo == "L" else F.T @ F) - S
+            record(f"potrf {uplo} n=2000 nb=256 factor", float(np.abs(F - tri(want)).max() / np.abs(tri(want)).max()),
+                   50 * eps)
+            record(f"potrf {uplo} n=2000 nb=256 backward", float(np.linalg.norm(R) / (n * np.linalg.norm(S))), 50 * eps)
+            ok_all = ok_all and info == 0 and info_ref == 0
+
+    # ---- posv: solution against the reference's, and the tester's residual ----
+    n, nrhs, nb = 2000, 10, 256
+    H = sl.HermitianMatrix("L", n, nb, p, q).generate(7, dominant=True)
+    Bm = sl.Matrix(n, nrhs, nb, p, q).generate(8)
+    info = sl.posv(H, Bm, lookahead=lookahead)
+    X = assemble(Bm)
+    H.free()
+    Bm.free()
+    if rank == 0:
+        A0 = ol.matgen(7, n, n)
+        A0[np.arange(n), np.arange(n)] += n
+        S = np.tril(A0) + np.tril(A0, -1).T
+        B0 = ol.matgen(8, n, nrhs)
+        if kind == "reference" and hasattr(L, "ref_posv_any"):
+            Af, Xr = A0.copy(order="F"), B0.copy(order="F")
+            L.ref_posv_any(0, ord("L"), n, nrhs, nb, Af.ctypes.data, n, Xr.ctypes.data, n, 1)
+        else:
+            Xr = np.linalg.solve(S, B0)
+        record("posv n=2000 nrhs=10 solution", float(np.abs(X - Xr).max() / np.abs(Xr).max()), 50 * eps)
+        record("posv n=2000 nrhs=10 residual",
+               float(np.linalg.norm(B0 - S @ X, 1) / (n * np.linalg.norm(S, 1) * np.linalg.norm(X, 1))), 25 * eps)
+        ok_all = ok_all and info == 0
+        out["checker"] = ("oracle/_ref: the unmodified reference, Target::HostTask" if kind == "reference"
+                          else "oracle port (oracle/_ref not built)")
+        out["max_err_eps"] = worst
+        out["ok"] = bool(ok_all)
+    return out if rank == 0 else None
 
 
 # ------------------------------------------------------------------------------------------
@@ -377,7 +500,7 @@ def main():
 
     # ---- zgemm, BASELINE.json configs[4]: complex<double>, nb = 384, ragged last tiles -------
     zg = None
-    if args.zgemm:
+    if not args.no_zgemm:
         nz, nbz = args.zgemm_n, 384
         za, zb = ALPHA + 1.4142135623730951j, BETA + 1.7320508075688772j
         Az = sl.Matrix(nz, nz, nbz, p, q, dtype=np.complex128).generate(1)
@@ -421,7 +544,7 @@ def main():
 
     # ---- herk / syrk tile-update microbench, BASELINE.json configs[3] (1 GPU) ---------------
     hk = None
-    if args.herk and world == 1:
+    if not args.no_herk and world == 1:
         nh = args.herk_n
         Ah = sl.Matrix(nh, nb, nb).generate(1, dist=2)
         hk = {"n": nh, "k": nb, "nb": nb, "flops": "k*n*(n+1) (blaspp flops.hh:128-132)"}
@@ -445,10 +568,14 @@ def main():
             Ch.free()
         Ah.free()
 
+    # ---- parity on this job's grid against the CPU reference (checker, untimed) ------------
+    parity = None
+    if not args.no_parity:
+        parity = multirank_parity(sl, world, rank, p, q, args.lookahead)
+
     # ---- CPU baseline: the reference's HostTask path on the host cores --------------------
     cpu = None
     if not args.no_cpu and rank == 0 and world == 1:
-        os.environ.setdefault("OMP_NUM_THREADS", str(os.cpu_count()))
         n_s, k_s = (16384, 8192) if n >= 16384 else (n, min(k, 4 * nb))
         tf_c, secs, cores, kind = time_reference_gemm(n_s, k_s, nb, 1)
         cpu = {"value": tf_c, "unit": "TFLOP/s", "cores": cores, "kind": kind,
@@ -457,11 +584,14 @@ def main():
 
     if rank == 0:
         launch_flops = flops / K / world      # one dgemm_tiles_kernel launch per step per GPU
+        # dram__bytes of ONE launch, from ncu captures at this launch shape (tiles per launch on
+        # one GPU); null when that shape has not been captured
         traffic = None
+        tiles_per_launch = ((n + nb - 1) // nb) ** 2 // world
         tfile = os.path.join(ROOT, "profiles", "dgemm_traffic_per_launch.json")
         if os.path.exists(tfile):
             try:
-                traffic = json.load(open(tfile)).get("dram_bytes_per_launch")
+                traffic = json.load(open(tfile)).get("dram_bytes_per_launch_by_tiles", {}).get(str(tiles_per_launch))
             except Exception:
                 traffic = None
         line = {
@@ -483,10 +613,12 @@ def main():
             "roofline": {"bound": "tensor", "achieved": launch_flops / (ms / K * 1e-3) * 1e-12,
                          "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": launch_flops / (ms / K * 1e-3) * 1e-12 / peak_tf,
-                         "traffic": traffic, "kernel": "dgemm_tiles_kernel",
+                         "traffic": traffic, "tiles_per_launch": tiles_per_launch,
+                         "kernel": "dgemm_tiles_kernel",
                          "peak_source": "measured in this run by te_peak_fp64 (register-resident "
                                         "DMMA.8x8x4); MEASURED_PEAKS.json has no FP64 entry"},
             "e2e": e2e, "cpu_baseline": cpu, "potrf": potrf, "zgemm": zg, "herk_microbench": hk,
+            "parity": parity,
         }
         print(json.dumps(line), flush=True)
     sl.finalize()

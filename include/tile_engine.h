@@ -294,6 +294,58 @@ int te_comm_allreduce_i64(te_comm* comm, int64_t* buf_dev, size_t count, int op,
 int te_comm_allreduce_f64(te_comm* comm, double* buf_dev, size_t count, int op, void* stream);
 
 /* ------------------------------------------------------------------------
+ * Copy-engine tile transport between the box's GPUs (one rank per GPU, every
+ * rank a process on the same box).  The default data plane of
+ * BaseMatrix::tileBcast / listBcast / listBcastMT when more than one rank runs.
+ *
+ * Replaces, like the NCCL calls above, the per-tile MPI messages of
+ *   tileBcastToSet / tileIbcastToSet   include/slate/BaseMatrix.hh:2283-2387
+ *   Tile::isend / irecv                include/slate/Tile.hh:1084-1200
+ * and, for several GPUs under one rank, the per-tile device-to-device
+ * cudaMemcpyAsync of Tile::copyData (include/slate/Tile.hh:971-1042,
+ * BaseMatrix.hh:2052-2097).  A tile moves as ONE cudaMemcpyAsync into memory
+ * of the destination GPU that the root's process has mapped with CUDA IPC,
+ * i.e. on a copy engine over NVLink; arrival is a sequence number written
+ * behind the data and waited for by a stream memory operation.  Neither side
+ * launches a kernel, so a broadcast never queues behind (or takes SMs from)
+ * the trailing update that is running.
+ *
+ * te_peer_open (collective over `comm`, synchronous) gives every rank an
+ * arena of `arena_bytes` of landing zones, opens every peer's arena and sets
+ * up a host mailbox in POSIX shared memory.  For message number s of the
+ * ordered pair (root, dest) -- both ranks count them from the same broadcast
+ * plan -- the calls are, in this order:
+ *   dest  te_peer_post(root, bytes, &s, &landing)   reserve + announce a zone
+ *   root  te_peer_fetch(dest, bytes, &s, &offset)   host wait for the zone
+ *         te_peer_put(dest, offset + o, tile, n, stream)   one per tile / run
+ *         te_peer_signal(dest, s, stream)           after the last put
+ *   dest  te_peer_wait(root, s, stream)             stream waits for arrival
+ *         ... device-to-device copies out of `landing` on `stream` ...
+ *         te_peer_consumed(root, s, stream)         zone reusable after this
+ * A message may not exceed te_peer_max_message() = arena / (2 * ranks) bytes:
+ * with every rank posting at most one message per peer before it copies the
+ * previous ones out, a post can always be satisfied by waiting for zones that
+ * are already being drained.  Host waits (post: ring full; fetch: zone not yet
+ * announced) give up after TE_PEER_TIMEOUT_S seconds (default 120) with
+ * TE_ERR_CUDA instead of hanging.  TE_PEER_MEMOPS=0 replaces the stream
+ * memory operations by a one-thread kernel (wait) and an 8-byte copy (signal).
+ * ---------------------------------------------------------------------- */
+int te_peer_open(te_comm* comm, size_t arena_bytes);
+int te_peer_close(te_comm* comm);             /* collective; te_comm_destroy calls it */
+int te_peer_is_open(const te_comm* comm);
+size_t te_peer_max_message(const te_comm* comm);
+int te_peer_post(te_comm* comm, int root, size_t bytes, uint64_t* seq, void** landing);
+int te_peer_fetch(te_comm* comm, int dest, size_t bytes, uint64_t* seq, uint64_t* offset);
+int te_peer_put(te_comm* comm, int dest, uint64_t offset, const void* src, size_t bytes,
+                void* stream);
+int te_peer_signal(te_comm* comm, int dest, uint64_t seq, void* stream);
+int te_peer_wait(te_comm* comm, int root, uint64_t seq, void* stream);
+int te_peer_consumed(te_comm* comm, int root, uint64_t seq, void* stream);
+/* counters since te_peer_open; memops: bit 0 = wait, bit 1 = signal by stream memory op */
+int te_peer_stats(const te_comm* comm, uint64_t* puts, uint64_t* put_bytes, uint64_t* signals,
+                  uint64_t* waits, int* memops);
+
+/* ------------------------------------------------------------------------
  * Harness kernels around the hot path (inputs and residual checks).
  *
  * te_matgen_tile reproduces matgen bit for bit on the device: entry (i, j) of

@@ -103,6 +103,7 @@ int64_t oracle_dgetrf_nopiv(int64_t m, int64_t n, int64_t nb, double* A, int64_t
 int64_t oracle_zgetrf_nopiv(int64_t m, int64_t n, int64_t nb, double* A, int64_t lda);
 
 int oracle_num_threads(void);
+void oracle_set_num_threads(int n);
 
 #ifdef __cplusplus
 }

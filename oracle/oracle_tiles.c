@@ -37,6 +37,7 @@ typedef double _Complex zc;
 static zc mkz(const double* p) { return p[0] + p[1] * I; }
 
 int oracle_num_threads(void) { return omp_get_max_threads(); }
+void oracle_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
 
 void oracle_tile_dgemm(int opa, int opb, int64_t m, int64_t n, int64_t k, double alpha,
                        const double* A, int64_t lda, const double* B, int64_t ldb,

@@ -334,6 +334,7 @@ extern "C" {
 
 const char* ref_version(void) { return "slate-ref 2023.11.05 HostTask single-rank"; }
 int ref_num_threads(void) { return omp_get_max_threads(); }
+void ref_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
 
 int ref_dgemm(int opa, int opb, int64_t m, int64_t n, int64_t k, int64_t nb, double alpha,
               double* A, int64_t lda, double* B, int64_t ldb, double beta, double* C, int64_t ldc,

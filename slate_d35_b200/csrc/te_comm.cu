@@ -9,24 +9,7 @@
 // send/recv pairs on the caller's stream: the root posts a send per destination rank,
 // each destination a recv into its workspace tile.  NVSwitch gives every pair full
 // bandwidth, so a flat fan-out needs no tree; device buffers only (no host staging).
-#include "te_common.cuh"
-#include <nccl.h>
-
-struct te_comm {
-    ncclComm_t nccl;
-    int rank, size, device;
-};
-
-namespace te {
-#define TE_NCCL_CHECK(expr)                                                  \
-    do {                                                                     \
-        ncclResult_t r_ = (expr);                                            \
-        if (r_ != ncclSuccess) {                                             \
-            te::set_last_error(#expr, ncclGetErrorString(r_));               \
-            return TE_ERR_NCCL;                                              \
-        }                                                                    \
-    } while (0)
-}
+#include "te_comm_internal.cuh"
 
 extern "C" int te_comm_unique_id(void* id_out, size_t bytes)
 {
@@ -50,6 +33,12 @@ extern "C" int te_comm_init_rank(const void* id, size_t bytes, int nranks, int r
     c->rank = rank;
     c->size = nranks;
     c->device = device;
+    c->peer = nullptr;
+    // every rank derives the same job tag from the id (names the shared-memory mailbox of
+    // the copy-engine transport, te_peer.cu)
+    uint64_t h = 1469598103934665603ull;
+    for (size_t b = 0; b < sizeof(uid); ++b) h = (h ^ (unsigned char)uid.internal[b]) * 1099511628211ull;
+    c->job_tag = h;
     ncclResult_t r = ncclCommInitRank(&c->nccl, nranks, uid, rank);
     if (r != ncclSuccess) {
         te::set_last_error("ncclCommInitRank", ncclGetErrorString(r));
@@ -88,6 +77,7 @@ extern "C" int te_comm_connect_all(te_comm* c, void* stream)
 extern "C" int te_comm_destroy(te_comm* c)
 {
     if (!c) return TE_OK;
+    if (c->peer) te_peer_close(c);
     ncclCommDestroy(c->nccl);
     delete c;
     return TE_OK;

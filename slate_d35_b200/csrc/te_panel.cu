@@ -687,6 +687,18 @@ static __device__ __align__(256) unsigned char te_trsm_static_scratch[TE_TRSM_ST
 
 namespace te {
 
+// the block must hold the scratch of the largest call the two limits allow, for both types
+// (keeps a change of te_tile_desc, IB or the limits from silently overrunning it)
+template <typename T>
+constexpr size_t trsm_static_need()
+{
+    constexpr size_t nblk = (TE_TRSM_STATIC_MAX_NA + PanelCfg<T>::IB - 1) / PanelCfg<T>::IB;
+    return nblk * PanelCfg<T>::IB * PanelCfg<T>::IB * sizeof(T)
+           + 2 * nblk * TE_TRSM_STATIC_MAX_COUNT * sizeof(te_tile_desc) + 256;
+}
+static_assert(trsm_static_need<double>() <= TE_TRSM_STATIC_SCRATCH_BYTES, "static trsm scratch too small (real)");
+static_assert(trsm_static_need<zd>() <= TE_TRSM_STATIC_SCRATCH_BYTES, "static trsm scratch too small (complex)");
+
 static std::mutex g_static_scratch_mu;
 static void* g_static_scratch_ptr[64] = {};
 

@@ -181,14 +181,18 @@ extern "C" int te_memset_async(void* dst, int value, size_t bytes, void* stream)
 // ---------------------------------------------------------------- device-tile pool
 // Fixed-size blocks carved from slabs.  reserve() adds ONE slab (a single cudaMalloc)
 // holding the requested blocks; alloc() pops a free block and, like the reference
-// (Memory.cc:118-141), grows by one block when the free list is empty.  Blocks are
-// 256-byte aligned (block_bytes is rounded up), so every tile keeps the 16-byte
-// cp.async fast path.
+// (Memory.cc:118-141), grows the pool by one block when the free list is empty -- as far
+// as available / capacity show.  Underneath, growth does NOT cost a cudaMalloc per block
+// (a synchronous call in the middle of a factorisation, the weakness of the reference's
+// pool): the pool mallocs max(16, capacity / 8) blocks at once and keeps the rest as
+// spares, which later growth steps take one at a time.  Blocks are 256-byte aligned
+// (block_bytes is rounded up), so every tile keeps the 16-byte cp.async fast path.
 struct te_pool {
     int device;
     size_t block_bytes;
     std::mutex mu;
     std::vector<void*> free_blocks;      // LIFO
+    std::vector<void*> spare;            // malloc'ed ahead by growth, not yet in circulation
     std::vector<void*> slabs;
     size_t capacity;
 };
@@ -223,17 +227,31 @@ extern "C" int te_pool_reserve(te_pool* p, int64_t nblocks)
 extern "C" int te_pool_alloc(te_pool* p, void** block)
 {
     if (!p || !block) return TE_ERR_ARG;
-    {
-        std::lock_guard<std::mutex> lock(p->mu);
-        if (!p->free_blocks.empty()) {
-            *block = p->free_blocks.back();
-            p->free_blocks.pop_back();
-            return TE_OK;
-        }
+    std::lock_guard<std::mutex> lock(p->mu);
+    if (!p->free_blocks.empty()) {
+        *block = p->free_blocks.back();
+        p->free_blocks.pop_back();
+        return TE_OK;
     }
-    int st = te_pool_reserve(p, 1);
-    if (st != TE_OK) return st;
-    return te_pool_alloc(p, block);
+    if (p->spare.empty()) {
+        // grow: one cudaMalloc for a chunk of blocks (fall back to a single block if the
+        // device cannot hold the chunk)
+        size_t chunk = p->capacity / 8 > 16 ? p->capacity / 8 : 16;
+        void* slab = nullptr;
+        int st = te_device_malloc(p->device, p->block_bytes * chunk, &slab);
+        if (st != TE_OK) {
+            chunk = 1;
+            st = te_device_malloc(p->device, p->block_bytes, &slab);
+            if (st != TE_OK) return st;
+        }
+        p->slabs.push_back(slab);
+        for (size_t i = chunk; i-- > 0;)
+            p->spare.push_back((char*)slab + i * p->block_bytes);
+    }
+    *block = p->spare.back();
+    p->spare.pop_back();
+    p->capacity += 1;            // Memory.cc:196-202: capacity counts the blocks in circulation
+    return TE_OK;
 }
 
 extern "C" int te_pool_free(te_pool* p, void* block)
@@ -264,6 +282,7 @@ extern "C" int te_pool_clear(te_pool* p)
         TE_CUDA_CHECK(cudaFree(s));
     p->slabs.clear();
     p->free_blocks.clear();
+    p->spare.clear();
     p->capacity = 0;
     return TE_OK;
 }

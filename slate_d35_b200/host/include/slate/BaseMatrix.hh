@@ -546,6 +546,8 @@ protected:
     void tileGet(int64_t i, int64_t j, int device, bool modify, int queue);
     void updateOrigin(int64_t i, int64_t j);
     void bcastCoalesced(std::vector<BcastOp> const& plan);
+    void bcastPeer(std::vector<BcastOp> const& plan);
+    Tile<scalar_t>* prepareToReceive(int64_t i, int64_t j);
     /// true if tile (i, j) has a valid device instance in the other layout
     bool needsConvert(int64_t i, int64_t j, LayoutConvert lc)
     {
@@ -698,47 +700,44 @@ void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
     }
 
     slate_assert(comm->nccl != nullptr);
-    // Opt-in: one message per (root, destination) pair instead of one per tile.  Written after
-    // the round's multi-GPU budget was spent: NOT YET RUN on GPUs, so off unless asked for.
-    static const bool coalesce = [] {
-        const char* e = std::getenv("SLATE_B200_BCAST_COALESCE");
-        return e && e[0] == '1';
-    }();
-    if (coalesce) {
+    // Data plane (slate::initialize, SLATE_B200_BCAST): copy engines over CUDA IPC by default,
+    // else NCCL send/recv -- one message per tile, or per (root, destination) pair.
+    if (comm->peer_plane) {
+        bcastPeer(bcastPlan(bcast_list));
+        return;
+    }
+    if (comm->nccl_coalesce) {
         bcastCoalesced(bcastPlan(bcast_list));
         return;
     }
     void* stream = eng.comm_stream();
+    auto plan = bcastPlan(bcast_list);
+    // Roots first: fetching / converting a tile may itself put work and a mark on the comm
+    // stream, and the receivers below are stamped with the mark that FOLLOWS the group.
+    for (auto const& op : plan) {
+        if (me != op.root) continue;
+        tileGet(op.i, op.j, 0, false, -1);
+        auto& node = storage_->at(globalIndex(op.i, op.j));
+        // tiles travel in ColMajor (the receivers' workspace tiles are)
+        if (node.dev->layout() != Layout::ColMajor)
+            tileLayoutConvert(op.i, op.j, 0, Layout::ColMajor, -1);
+        // (a host-to-device staging copy just enqueued is on the same comm stream, ahead
+        //  of the sends: stream order is enough)
+        eng.comm_wait_queue_seq(node.write_queue, node.write_seq);
+        // device instances made by this library are contiguous (stride == mb)
+        slate_assert(node.dev->isContiguous());
+    }
     bool any = false;
-    for (auto const& op : bcastPlan(bcast_list)) {
+    for (auto const& op : plan) {
         const int64_t i = op.i, j = op.j;
         if (me == op.root) {
-            tileGet(i, j, 0, false, -1);
-            auto& node = storage_->at(globalIndex(i, j));
-            // tiles travel in ColMajor (the receivers' workspace tiles are)
-            if (node.dev->layout() != Layout::ColMajor)
-                tileLayoutConvert(i, j, 0, Layout::ColMajor, -1);
-            // (a host-to-device staging copy just enqueued is on the same comm stream, ahead
-            //  of the sends: stream order is enough)
-            eng.comm_wait_queue_seq(node.write_queue, node.write_seq);
-            Tile<scalar_t>* t = node.dev;
+            Tile<scalar_t>* t = storage_->at(globalIndex(i, j)).dev;
             if (!any) { slate_te_call(te_comm_group_start()); any = true; }
-            // device instances made by this library are contiguous (stride == mb)
-            slate_assert(t->isContiguous());
             for (int r : op.dests)
                 slate_te_call(te_comm_send(comm->nccl, t->data(), t->bytes(), r, stream));
         }
         else if (std::find(op.dests.begin(), op.dests.end(), me) != op.dests.end()) {
-            // tilePrepareToReceive (MatrixStorage.hh:406-420): workspace tile on the device
-            auto* node = storage_->find(globalIndex(i, j));
-            if (!node || !node->dev)
-                storage_->tileInsert(globalIndex(i, j), 0, TileKind::Workspace);
-            auto& nd = storage_->at(globalIndex(i, j));
-            nd.receive_count += 1;
-            nd.dev_state = MOSI::Shared;
-            nd.write_queue = -1;
-            nd.comm_seq = eng.next_comm_seq();
-            Tile<scalar_t>* t = nd.dev;
+            Tile<scalar_t>* t = prepareToReceive(i, j);
             if (!any) { slate_te_call(te_comm_group_start()); any = true; }
             slate_te_call(te_comm_recv(comm->nccl, t->data(), t->bytes(), op.root, stream));
         }
@@ -752,6 +751,171 @@ void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
         eng.mark_comm();
         device_copies_pending_ = false;
     }
+}
+
+//------------------------------------------------------------------------------
+/// tilePrepareToReceive (MatrixStorage.hh:406-420): the workspace tile a broadcast fills, stamped
+/// with the comm-stream mark that will follow the transfer.  A device instance that already
+/// exists is reused; launches that may still read it were enqueued before this call, so the
+/// comm stream is put behind all compute queues first (the drivers release a panel before it
+/// is broadcast again, so this is the rare path), and a leftover RowMajor layout is reset.
+template <typename scalar_t>
+Tile<scalar_t>* BaseMatrix<scalar_t>::prepareToReceive(int64_t i, int64_t j)
+{
+    Engine& eng = Engine::instance();
+    const ij_tuple gij = globalIndex(i, j);
+    auto* node = storage_->find(gij);
+    if (!node || !node->dev)
+        storage_->tileInsert(gij, 0, TileKind::Workspace);
+    else {
+        eng.comm_wait_all_queues();
+        if (node->dev->layout() != Layout::ColMajor && node->dev->kind() != TileKind::UserOwned)
+            node->dev->setLayout(Layout::ColMajor, node->dev->mb());
+    }
+    auto& nd = storage_->at(gij);
+    nd.receive_count += 1;
+    nd.dev_state = MOSI::Shared;
+    nd.write_queue = -1;
+    nd.comm_seq = eng.next_comm_seq();
+    return nd.dev;
+}
+
+//------------------------------------------------------------------------------
+/// listBcastMT on the copy engines (tile_engine.h te_peer_*): per (root, destination) pair the
+/// tiles of the list travel as messages of at most te_peer_max_message() bytes.  Message c of
+/// every pair is handled in round c: this rank first announces a landing zone for each message
+/// it expects, then pushes the messages it owes (peer copies + arrival flag), then makes its
+/// comm stream wait for the arrivals and copy the tiles out of the landing zones into their
+/// workspace blocks.  Pushes are enqueued BEFORE the waits of the same round, and every rank
+/// walks the same lists in the same order, so no stream ever waits for a push that sits behind
+/// it.  No kernel is launched on either side.
+template <typename scalar_t>
+void BaseMatrix<scalar_t>::bcastPeer(std::vector<BcastOp> const& plan)
+{
+    Engine& eng = Engine::instance();
+    Comm* comm = storage_->comm_;
+    const int me = comm->rank;
+    void* stream = eng.comm_stream();
+    std::vector<PairMsg> sends, recvs;
+    bcastPairs(plan, me, &sends, &recvs);
+    if (sends.empty() && recvs.empty()) {
+        if (device_copies_pending_) { eng.mark_comm(); device_copies_pending_ = false; }
+        return;
+    }
+    auto align256 = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    auto op_bytes = [&](size_t o) {
+        return sizeof(scalar_t) * (size_t)tileMb(plan[o].i) * (size_t)tileNb(plan[o].j);
+    };
+    const size_t max_msg = te_peer_max_message(comm->nccl);
+
+    // messages -> chunks of consecutive tiles, each tile at a 256-byte aligned offset; root and
+    // destination cut the same list the same way
+    struct Chunk { size_t first, last, bytes; };
+    auto cut = [&](PairMsg const& m) {
+        std::vector<Chunk> v;
+        size_t cur = 0, first = 0;
+        for (size_t t = 0; t < m.ops.size(); ++t) {
+            const size_t b = align256(op_bytes(m.ops[t]));
+            if (b > max_msg)
+                slate_error("broadcast: one tile exceeds the peer arena's message limit; "
+                            "raise SLATE_B200_ARENA_MB");
+            if (cur + b > max_msg) {
+                v.push_back({first, t, cur});
+                first = t;
+                cur = 0;
+            }
+            cur += b;
+        }
+        v.push_back({first, m.ops.size(), cur});
+        return v;
+    };
+    std::vector<std::vector<Chunk>> send_chunks, recv_chunks;
+    size_t rounds = 0;
+    for (auto const& m : sends) { send_chunks.push_back(cut(m)); rounds = std::max(rounds, send_chunks.back().size()); }
+    for (auto const& m : recvs) { recv_chunks.push_back(cut(m)); rounds = std::max(rounds, recv_chunks.back().size()); }
+
+    // roots: tiles valid on the device, ColMajor, the comm stream behind their producers
+    std::vector<char> prepared(plan.size(), 0);
+    for (auto const& m : sends)
+        for (size_t o : m.ops) {
+            if (prepared[o]) continue;
+            prepared[o] = 1;
+            const int64_t i = plan[o].i, j = plan[o].j;
+            tileGet(i, j, 0, false, -1);
+            auto& node = storage_->at(globalIndex(i, j));
+            if (node.dev->layout() != Layout::ColMajor) tileLayoutConvert(i, j, 0, Layout::ColMajor, -1);
+            eng.comm_wait_queue_seq(node.write_queue, node.write_seq);
+        }
+    // destinations: workspace tiles, stamped with the mark at the end of this call
+    std::vector<Tile<scalar_t>*> dst_tile(plan.size(), nullptr);
+    for (auto const& m : recvs)
+        for (size_t o : m.ops) dst_tile[o] = prepareToReceive(plan[o].i, plan[o].j);
+
+    eng.trace_begin(-1, "bcast_peer", (int64_t)plan.size());
+    struct Landed { size_t r; uint64_t seq; char* zone; };
+    std::vector<Landed> landed;
+    for (size_t c = 0; c < rounds; ++c) {
+        // 1. announce where this round's incoming messages go
+        landed.clear();
+        for (size_t r = 0; r < recvs.size(); ++r) {
+            if (c >= recv_chunks[r].size()) continue;
+            uint64_t seq = 0;
+            void* zone = nullptr;
+            slate_te_call(te_peer_post(comm->nccl, recvs[r].peer, recv_chunks[r][c].bytes, &seq, &zone));
+            landed.push_back({r, seq, (char*)zone});
+        }
+        // 2. push what this rank owes: runs of tiles adjacent in memory go as one copy
+        for (size_t s = 0; s < sends.size(); ++s) {
+            if (c >= send_chunks[s].size()) continue;
+            Chunk const& ch = send_chunks[s][c];
+            uint64_t seq = 0, off = 0;
+            slate_te_call(te_peer_fetch(comm->nccl, sends[s].peer, ch.bytes, &seq, &off));
+            const char* run_src = nullptr;
+            size_t run_bytes = 0, run_off = 0, o_off = 0;
+            auto flush = [&]() {
+                if (run_bytes)
+                    slate_te_call(te_peer_put(comm->nccl, sends[s].peer, off + run_off, run_src, run_bytes, stream));
+                run_bytes = 0;
+            };
+            for (size_t t = ch.first; t < ch.last; ++t) {
+                Tile<scalar_t>* tile = storage_->at(globalIndex(plan[sends[s].ops[t]].i, plan[sends[s].ops[t]].j)).dev;
+                const size_t b = tile->bytes();
+                if (!tile->isContiguous())
+                    slate_error("broadcast: strided device tile (user-owned device tiles must have stride == mb)");
+                const bool joins = run_bytes && run_src + run_bytes == (const char*)tile->data()
+                                   && run_off + run_bytes == o_off;
+                if (!joins) {
+                    flush();
+                    run_src = (const char*)tile->data();
+                    run_off = o_off;
+                }
+                run_bytes += b;
+                o_off += align256(b);
+            }
+            flush();
+            slate_te_call(te_peer_signal(comm->nccl, sends[s].peer, seq, stream));
+        }
+        // 3. arrivals: wait, copy out, give the landing zone back
+        for (auto const& l : landed) {
+            Chunk const& ch = recv_chunks[l.r][c];
+            slate_te_call(te_peer_wait(comm->nccl, recvs[l.r].peer, l.seq, stream));
+            size_t o_off = 0;
+            for (size_t t = ch.first; t < ch.last; ++t) {
+                Tile<scalar_t>* tile = dst_tile[recvs[l.r].ops[t]];
+                if (tile->isContiguous())
+                    slate_te_call(te_memcpy_async(tile->data(), l.zone + o_off, tile->bytes(), TE_COPY_D2D, stream));
+                else
+                    slate_te_call(te_memcpy2d_async(tile->data(), sizeof(scalar_t) * tile->stride(), l.zone + o_off,
+                                                    sizeof(scalar_t) * tile->mb(), sizeof(scalar_t) * tile->mb(),
+                                                    tile->nb(), TE_COPY_D2D, stream));
+                o_off += align256(tile->bytes());
+            }
+            slate_te_call(te_peer_consumed(comm->nccl, recvs[l.r].peer, l.seq, stream));
+        }
+    }
+    eng.trace_end(-1);
+    eng.mark_comm();
+    device_copies_pending_ = false;
 }
 
 //------------------------------------------------------------------------------
@@ -792,16 +956,7 @@ void BaseMatrix<scalar_t>::bcastCoalesced(std::vector<BcastOp> const& plan)
         }
     // destinations: workspace tiles (tilePrepareToReceive)
     for (auto const& m : recvs)
-        for (size_t o : m.ops) {
-            const ij_tuple gij = globalIndex(plan[o].i, plan[o].j);
-            auto* node = storage_->find(gij);
-            if (!node || !node->dev) storage_->tileInsert(gij, 0, TileKind::Workspace);
-            auto& nd = storage_->at(gij);
-            nd.receive_count += 1;
-            nd.dev_state = MOSI::Shared;
-            nd.write_queue = -1;
-            nd.comm_seq = eng.next_comm_seq();
-        }
+        for (size_t o : m.ops) prepareToReceive(plan[o].i, plan[o].j);
 
     // which messages need staging
     auto adjacent = [&](PairMsg const& m) {

@@ -41,6 +41,11 @@ struct Comm {
     te_comm* nccl = nullptr;
     int rank = 0;
     int size = 1;
+    /// data plane of the tile broadcasts (slate::initialize; SLATE_B200_BCAST=peer|nccl|coalesce):
+    /// copy engines over CUDA IPC (te_peer_*, the default), NCCL send/recv per tile, or NCCL
+    /// send/recv per (root, destination) pair
+    bool peer_plane = false;
+    bool nccl_coalesce = false;
 };
 
 /// MPI_COMM_WORLD of this process (set by slate::initialize; single rank by default).
@@ -150,6 +155,8 @@ public:
     void* scratch(int q, size_t bytes);
     /// One device int per (queue, slot) for potrf's info.
     int* info_slot(int index);
+    int* info_scratch_slot();
+    void reserve_info_slots(int64_t n);
 
     // ---- deferred actions (release of workspace tiles) ----
     /// Runs fn once everything enqueued so far on the given queues (bit q) and, if
@@ -204,6 +211,7 @@ private:
     void* scratch_[MaxQueues] = {};
     size_t scratch_bytes_[MaxQueues] = {};
     int* info_base_ = nullptr;
+    int info_cap_ = 4096;
     static const int CommSlabs = 4;
     CommSlab comm_slab_[CommSlabs];
     int comm_slab_next_ = 0;

@@ -260,7 +260,7 @@ int64_t potrf(HermitianMatrix<scalar_t>& A_in, Options const& opts)
     if (A.uplo() == Uplo::Upper)
         A = conj_transpose(A);
     const int64_t A_nt = A.nt();
-    slate_assert(A_nt < 4095);
+    Engine::instance().reserve_info_slots(A_nt);      // one device info per block column
 
     A.allocateBatchArrays(0, queue_la0 + lookahead);
     A.reserveDeviceWorkspace();

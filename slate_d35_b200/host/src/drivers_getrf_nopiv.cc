@@ -58,7 +58,7 @@ int64_t getrf_nopiv(Matrix<scalar_t>& A, Options const& opts)
 
     const int64_t A_mt = A.mt(), A_nt = A.nt();
     const int64_t min_mt_nt = std::min(A_mt, A_nt);
-    slate_assert(min_mt_nt < 4095);
+    Engine::instance().reserve_info_slots(min_mt_nt);
     if (min_mt_nt == 0) return 0;
 
     // src/getrf_nopiv.cc:43-48

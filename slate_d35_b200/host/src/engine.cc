@@ -118,7 +118,7 @@ void Engine::initialize(int device)
     slate_te_call(te_stream_create(device_, 1, &comm_stream_));
     slate_te_call(te_event_create(device_, 0, &comm_event_));
     void* p = nullptr;
-    slate_te_call(te_device_malloc(device_, sizeof(int) * 4096, &p));
+    slate_te_call(te_device_malloc(device_, sizeof(int) * (size_t)(info_cap_ + 1), &p));
     info_base_ = (int*)p;
 }
 
@@ -343,8 +343,29 @@ void* Engine::scratch(int q, size_t bytes)
 
 int* Engine::info_slot(int index)
 {
-    slate_assert(index >= 0 && index < 4096 && info_base_);
+    slate_assert(index >= 0 && index < info_cap_ && info_base_);
     return info_base_ + index;
+}
+
+/// The slot internal::potrf / getrf_nopiv use when the caller passes no device_info.
+int* Engine::info_scratch_slot()
+{
+    slate_assert(info_base_);
+    return info_base_ + info_cap_;
+}
+
+/// Makes info_slot(0 .. n-1) valid (one slot per block column of a factorisation).  Growing
+/// waits for the device: the old array may still be written by enqueued panel kernels.
+void Engine::reserve_info_slots(int64_t n)
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    if (n <= info_cap_ || !info_base_) return;
+    sync_all();
+    slate_te_call(te_device_free(device_, info_base_));
+    info_cap_ = (int)(n + n / 2);
+    void* p = nullptr;
+    slate_te_call(te_device_malloc(device_, sizeof(int) * (size_t)(info_cap_ + 1), &p));
+    info_base_ = (int*)p;
 }
 
 void* Engine::new_event(bool timing)
@@ -544,6 +565,21 @@ void initialize(int device, int rank, int size, const void* nccl_id)
         slate_te_call(te_comm_init_rank(nccl_id, TE_COMM_ID_BYTES, size, rank,
                                         Engine::instance().device(), &g_world.nccl));
         slate_te_call(te_comm_connect_all(g_world.nccl, Engine::instance().comm_stream()));
+        // Broadcast data plane.  Default: copy engines over CUDA IPC, no SM used (te_peer_*).
+        const char* plane = std::getenv("SLATE_B200_BCAST");
+        const char* old_switch = std::getenv("SLATE_B200_BCAST_COALESCE");
+        std::string mode = plane ? plane : (old_switch && old_switch[0] == '1') ? "coalesce" : "peer";
+        g_world.peer_plane = g_world.nccl_coalesce = false;
+        if (mode == "peer") {
+            size_t mb = 512;
+            if (const char* e = std::getenv("SLATE_B200_ARENA_MB")) mb = (size_t)std::atoll(e);
+            slate_te_call(te_peer_open(g_world.nccl, mb << 20));
+            g_world.peer_plane = te_peer_is_open(g_world.nccl) != 0;
+        }
+        else if (mode == "coalesce")
+            g_world.nccl_coalesce = true;
+        else if (mode != "nccl")
+            slate_error("SLATE_B200_BCAST must be peer, nccl or coalesce");
     }
 }
 
@@ -556,6 +592,7 @@ void finalize()
     }
     g_world.rank = 0;
     g_world.size = 1;
+    g_world.peer_plane = g_world.nccl_coalesce = false;
 }
 
 }  // namespace slate

@@ -661,7 +661,7 @@ int64_t potrf(TargetType<Target::Devices>, HermitianMatrix<scalar_t>& A, int pri
     A.tileGetForWriting(one, device, LayoutConvert::ColMajor, q);
     auto A00 = A(0, 0, device);
     const int dtype = te_dtype_of<scalar_t>::value;
-    int* info_dev = device_info ? device_info : eng.info_slot(4095);
+    int* info_dev = device_info ? device_info : eng.info_scratch_slot();
     size_t sb = te_potrf_scratch_bytes(dtype);
     // the trsm that follows on the same queue uses the same scratch: stream order keeps them apart
     void* scratch = eng.scratch(q, sb);
@@ -696,7 +696,7 @@ int64_t getrf_nopiv(TargetType<Target::Devices>, Matrix<scalar_t>& A, int64_t ib
     A.tileGetForWriting(one, device, LayoutConvert::ColMajor, q);
     auto A00 = A(0, 0, device);
     const int dtype = te_dtype_of<scalar_t>::value;
-    int* info_dev = device_info ? device_info : eng.info_slot(4095);
+    int* info_dev = device_info ? device_info : eng.info_scratch_slot();
     size_t sb = te_getrf_nopiv_scratch_bytes(dtype);
     void* scratch = eng.scratch(q, sb);
     eng.trace_begin(q, "getrf_nopiv_tile", 1);

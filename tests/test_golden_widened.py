@@ -97,18 +97,18 @@ def test_c_oracle_matches_reference_output(name, spec):
         f(1 if k == "her2k" else 0, ord(spec["uplo"]), ord(spec["opa"]), spec["n"], spec["k"], nb, sc(a),
           ol.P(y["A"]), y["A"].shape[0], ol.P(y["B"]), y["B"].shape[0], sc(beta), ol.P(y["C"]), spec["n"])
         tri = np.tril if spec["uplo"] == "L" else np.triu
-        assert np.abs(tri(y["C"]) - tri(gold)).max() <= 2 * tolerance(spec, np.abs(gold).max())
+        assert np.abs(tri(y["C"]) - tri(gold)).max() <= tolerance(spec, np.abs(gold).max())
         other = (lambda q: np.triu(q, 1)) if spec["uplo"] == "L" else (lambda q: np.tril(q, -1))
         assert np.array_equal(other(y["C"]), other(gold))
     elif k in ("hemm", "symm"):
         f = O.oracle_zhemm if z else O.oracle_dhemm
         f(1 if k == "hemm" else 0, ord(spec["side"]), ord(spec["uplo"]), spec["m"], spec["n"], nb, sc(a),
           ol.P(y["A"]), y["A"].shape[0], ol.P(y["B"]), spec["m"], sc(b), ol.P(y["C"]), spec["m"])
-        assert np.abs(y["C"] - gold).max() <= 2 * tolerance(spec, np.abs(gold).max())
+        assert np.abs(y["C"] - gold).max() <= tolerance(spec, np.abs(gold).max())
     else:
         f = O.oracle_zgetrf_nopiv if z else O.oracle_dgetrf_nopiv
         assert f(spec["m"], spec["n"], nb, ol.P(y["A"]), spec["m"]) == 0
-        assert np.abs(y["A"] - gold).max() <= 200 * EPS * np.abs(gold).max()
+        assert np.abs(y["A"] - gold).max() <= 50 * EPS * np.abs(gold).max()
 
 
 # ------------------------------------------------------------------------------------------
@@ -171,21 +171,21 @@ def run_b200(sl, spec, x):
 @pytest.mark.gpu
 @pytest.mark.parametrize("name,spec", CASES, ids=[n for n, _ in CASES])
 def test_b200_driver_matches_reference_output(sl, name, spec):
-    """same inputs, the B200 driver against what the reference returned: both are within the
-    reference's own test tolerance of the exact result, so within twice of each other; the parts
+    """same inputs, the B200 driver against what the reference returned: held to the reference's own
+    test tolerance (3 sqrt(k) eps for the updates, 50 eps for factors and solves); the parts
     the reference leaves alone (other triangle, strictly other part of a factor) must be equal"""
     x = wc.inputs(spec, lambda seed, m, n, dt: ol.matgen(seed, m, n, dt))
     res = run_b200(sl, spec, x)
     check_against(spec, x, res, False)
     gold, k = GOLD[name], spec["kind"]
     if k in ("hemm", "symm", "gemmA"):
-        assert np.abs(res - gold).max() <= 2 * tolerance(spec, np.abs(gold).max())
+        assert np.abs(res - gold).max() <= tolerance(spec, np.abs(gold).max())
     elif k in ("herk", "syrk", "her2k", "syr2k"):
         tri = np.tril if spec["uplo"] == "L" else np.triu
-        assert np.abs(tri(res) - tri(gold)).max() <= 2 * tolerance(spec, np.abs(gold).max())
+        assert np.abs(tri(res) - tri(gold)).max() <= tolerance(spec, np.abs(gold).max())
     elif k == "trsm":
         T = (np.tril if spec["uplo"] == "L" else np.triu)(x["A"])
-        assert np.abs(res - gold).max() <= 100 * EPS * np.abs(gold).max() * np.linalg.cond(T, 1)
+        assert np.abs(res - gold).max() <= 50 * EPS * np.abs(gold).max() * np.linalg.cond(T, 1)
     elif k in ("posv", "getrf_nopiv"):
         # factors of a diagonally dominant matrix: well conditioned, compare entry by entry
         mask = np.ones(gold.shape, dtype=bool)
@@ -194,4 +194,4 @@ def test_b200_driver_matches_reference_output(sl, name, spec):
             stored = np.tril(np.ones((n, n), dtype=bool)) if spec["uplo"] == "L" else np.triu(np.ones((n, n), dtype=bool))
             mask[:, :n] = stored
             assert np.array_equal(res[:, :n][~stored], gold[:, :n][~stored])
-        assert np.abs(res[mask] - gold[mask]).max() <= 200 * EPS * np.abs(gold[mask]).max()
+        assert np.abs(res[mask] - gold[mask]).max() <= 50 * EPS * np.abs(gold[mask]).max()

@@ -114,7 +114,7 @@ def run_gemm(te, dtype, opa, opb, m, n, k, alpha, beta, flags=0, count=2, inline
         scale = max(1.0, np.abs(want[:m]).max())
         kk = k * (4 if dtype == np.complex128 else 1)
         err = np.abs(got[:m] - want[:m]).max() / scale
-        assert err <= 3 * np.sqrt(max(kk, 1)) * EPS * 2, (err, opa, opb, m, n, k)
+        assert err <= 3 * np.sqrt(max(kk, 1)) * EPS, (err, opa, opb, m, n, k)
 
 
 @pytest.mark.parametrize("opa", "NT")
