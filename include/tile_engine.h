@@ -150,7 +150,8 @@ typedef struct te_tile_desc {
  * desc:   DEVICE array of `count` descriptors (upload it on `stream` first).
  * max_m/max_n: upper bounds of m and n over the batch (sizes the work grid).
  * alpha/beta: HOST pointers to one double (TE_F64) or two (TE_C64).
- * beta == 0 means C is not read (NaN-safe, as in BLAS).
+ * beta == 0 means C is not read (NaN-safe, as in BLAS).  As in BLAS, C_i must not
+ * overlap A_i or B_i.
  * opa/opb: TE_OP_N / T / C.  For TE_F64, T and C are the same.
  */
 int te_gemm_batched(int device, void* stream, int dtype, int opa, int opb,

@@ -33,24 +33,59 @@
 //     vectors forming 64-byte column segments per quad.
 #include "te_common.cuh"
 #include <stdlib.h>
+#include <string.h>
 
 namespace te {
 
 constexpr int BM = 128;
-constexpr int BN = 128;
+constexpr int BN = 128;                            // widest CTA tile (also the complex kernel's)
 constexpr int KC = 16;
-constexpr int STAGES = 5;
-constexpr int NCONSUMERS = 8;                      // consumer warps
-constexpr int NPRODUCERS = 4;                      // producer warps (one warpgroup)
+constexpr int NCONSUMERS = 8;                      // complex kernel: consumer warps
+constexpr int NPRODUCERS = 4;                      //                 producer warps
 constexpr int NTHREADS = (NCONSUMERS + NPRODUCERS) * 32;
-constexpr int REGS_PRODUCER = 56;                  // setmaxnreg budgets: 56*128 + 224*256
-constexpr int REGS_CONSUMER = 224;                 //   = 168*384 (the launch allocation)
-constexpr int LD_MN = BM + 4;            // row stride (doubles) of an [k][mn] slice
+constexpr int REGS_PRODUCER = 56;                  // setmaxnreg budgets: 56*P + 224*C = 168*(P+C)
+constexpr int REGS_CONSUMER = 224;                 //   for C = 2P consumer / producer threads
 constexpr int LD_K = KC + 4;             // row stride (doubles) of an [mn][k] slice
-constexpr int SLICE_MN = KC * LD_MN;     // 2112 doubles
-constexpr int SLICE_K = BM * LD_K;       // 2560 doubles
-constexpr int SLICE = (SLICE_MN > SLICE_K) ? SLICE_MN : SLICE_K;
-constexpr int SMEM_BYTES = STAGES * 2 * SLICE * (int)sizeof(double) + 2 * STAGES * 8;
+
+// Shape of the real kernel.  Three are built:
+//   Wide      128x128 CTA tile, 8 consumer + 4 producer warps, 5-stage ring, ONE CTA per SM;
+//   Pair      128x64  CTA tile, 4 consumer + 2 producer warps, 3-stage ring, TWO CTAs per SM;
+//   PairFull  as Pair, with two idle warps completing the producer warpgroup (below).
+// The warp tile (64x32, 128 accumulator registers) and the DMMA / LDS mix are the same.  With
+// one CTA per SM all eight consumer warps reach the epilogue of a block together and the tensor
+// pipe idles while C is read, scaled and written (ncu: pipe active 88.5 %, long-scoreboard
+// stalls 21 %); two independent CTAs per SM drift apart, so one CTA's epilogue, pipeline refill
+// and work-item decode run under the other's DMMA stream.  The price is 1.5x the L2 -> shared
+// traffic per flop (A slice per 64 columns instead of 128), far below what L2 delivers.
+template <int BN_, int NCONS_, int NPROD_, int STAGES_, int CTAS_PER_SM_, int NIDLE_ = 0,
+          int REGS_C_ = REGS_CONSUMER, int REGS_P_ = REGS_PRODUCER>
+struct DCfg {
+    static constexpr int BNv = BN_;
+    static constexpr int NCONS = NCONS_;
+    static constexpr int NPROD = NPROD_;
+    static constexpr int NIDLE = NIDLE_;         // warps that only complete the producer warpgroup
+    static constexpr int REGS_C = REGS_C_, REGS_P = REGS_P_;
+    static constexpr int STAGES = STAGES_;
+    static constexpr int CTAS_PER_SM = CTAS_PER_SM_;
+    static constexpr int THREADS = (NCONS_ + NPROD_ + NIDLE_) * 32;
+    static constexpr int LD_A = BM + 4;      // row stride (doubles) of a [k][m] slice of A
+    static constexpr int LD_B = BN_ + 4;     //                         a [k][n] slice of B
+    static constexpr int SLICE_A = (KC * LD_A > BM * LD_K) ? KC * LD_A : BM * LD_K;
+    static constexpr int SLICE_B = (KC * LD_B > BN_ * LD_K) ? KC * LD_B : BN_ * LD_K;
+    static constexpr int SMEM = STAGES_ * (SLICE_A + SLICE_B) * (int)sizeof(double) + 2 * STAGES_ * 8;
+    static_assert(NCONS_ == 2 * (BN_ / 32), "consumer warps tile the block as 2 (m) x BN/32 (n)");
+    // registers per thread at launch (multiple of 8) and the pool setmaxnreg redistributes
+    static constexpr int LAUNCH_REGS = (65536 / (THREADS * CTAS_PER_SM_)) / 8 * 8;
+    static_assert(REGS_P_ * (NPROD_ + NIDLE_) + REGS_C_ * NCONS_ <= LAUNCH_REGS * (NCONS_ + NPROD_ + NIDLE_),
+                  "setmaxnreg budget");
+};
+using CfgWide = DCfg<128, 8, 4, 5, 1>;
+// Pair: the producer "warpgroup" has two warps only (192 threads per CTA).
+using CfgPair = DCfg<64, 4, 2, 3, 2>;
+// PairFull: two idle warps complete the producer warpgroup (setmaxnreg is specified per
+// warpgroup of four warps); they give their registers back and exit.  256 threads per CTA,
+// 128 registers per thread at launch, so the consumers get 200 instead of 224.
+using CfgPairFull = DCfg<64, 4, 2, 3, 2, 2, 200, 56>;
 
 struct GemmParams {
     const te_tile_desc* desc;      // device array (batched mode)
@@ -75,7 +110,7 @@ struct Item {
     bool a16, b16, c16;            // 16-byte path usable
 };
 
-template <bool INL, int BMv = 128>
+template <bool INL, int BMv = 128, int BNv = 128>
 __device__ __forceinline__ bool decode(const GemmParams& p, int64_t w, Item& it)
 {
     const int bpt = p.nbm * p.nbn;
@@ -85,13 +120,13 @@ __device__ __forceinline__ bool decode(const GemmParams& p, int64_t w, Item& it)
     const int sm = sub - sn * p.nbm;
     const te_tile_desc* d = INL ? &p.inl[t] : &p.desc[t];
     const int m = d->m, n = d->n;
-    const int m0 = sm * BMv, n0 = sn * BN;
+    const int m0 = sm * BMv, n0 = sn * BNv;
     if (m0 >= m || n0 >= n)
         return false;
     const int flags = d->flags;
     if ((flags & TE_TILE_LOWER) && (m0 + BMv - 1 < n0))
         return false;
-    if ((flags & TE_TILE_UPPER) && (n0 + BN - 1 < m0))
+    if ((flags & TE_TILE_UPPER) && (n0 + BNv - 1 < m0))
         return false;
     it.m = m - m0;
     it.n = n - n0;
@@ -121,7 +156,7 @@ __device__ __forceinline__ bool decode(const GemmParams& p, int64_t w, Item& it)
 // tiles), which keeps the A / B tiles they share resident in L2; giving each CTA a
 // contiguous run instead spread the SMs over 148 different tiles and cost 1.6x more
 // DRAM reads (ncu, profiles/).
-template <bool INL, int BMv = 128>
+template <bool INL, int BMv = 128, int BNv = 128>
 struct Walker {
     int64_t w;
     int left;      // items this CTA may still take
@@ -134,7 +169,7 @@ struct Walker {
     {
         valid = false;
         while (left > 0 && w < p.total_work) {
-            if (decode<INL, BMv>(p, w, it)) {
+            if (decode<INL, BMv, BNv>(p, w, it)) {
                 valid = true;
                 nk = (it.k + KC - 1) / KC;
                 return;
@@ -164,22 +199,23 @@ struct Walker {
 // extents from there (anything beyond is zero-filled).
 //   KMAJOR == false: global (x, kk) at g[x + kk*ld]  -> smem [kk][LD_MN]
 //   KMAJOR == true : global (x, kk) at g[kk + x*ld]  -> smem [x][LD_K]
-template <bool KMAJOR>
+template <bool KMAJOR, int X, int LD_MNv, int NPROD>
 __device__ __forceinline__ void load_slice(double* s, const double* g, int ld,
                                            int x_rem, int k_rem, bool al16, int ptid)
 {
     const uint32_t sbase = smem_u32(s);
-    constexpr int NCHUNK = BM * KC / 2;          // 16-byte chunks per slice
+    constexpr int NCHUNK = X * KC / 2;           // 16-byte chunks per slice
+    constexpr int HALF = X / 2;                  // chunks per k row of an [k][mn] slice
 #pragma unroll
-    for (int i = 0; i < NCHUNK / (NPRODUCERS * 32); ++i) {
-        const int c = ptid + i * (NPRODUCERS * 32);
+    for (int i = 0; i < NCHUNK / (NPROD * 32); ++i) {
+        const int c = ptid + i * (NPROD * 32);
         int row, col, nv;
         uint32_t soff;
         if (!KMAJOR) {
-            row = c >> 6;              // kk
-            col = (c & 63) * 2;        // x
+            row = c / HALF;            // kk
+            col = (c % HALF) * 2;      // x
             nv = (row < k_rem) ? min(max(x_rem - col, 0), 2) : 0;
-            soff = (uint32_t)(row * LD_MN + col);
+            soff = (uint32_t)(row * LD_MNv + col);
         }
         else {
             row = c >> 3;              // x
@@ -205,14 +241,20 @@ __device__ __forceinline__ void load_slice(double* s, const double* g, int ld,
 // full[s] completes when the 128 producer threads' copies of stage s have
 // landed; empty[s] when the 8 consumer warps have finished reading it.  There
 // is no CTA-wide barrier in the loop.
-template <bool TA, bool TB, bool INL>
-__global__ void __launch_bounds__(NTHREADS, 1)
+template <bool TA, bool TB, bool INL, typename Cfg>
+__global__ void __launch_bounds__(Cfg::THREADS, Cfg::CTAS_PER_SM)
 dgemm_tiles_kernel(const __grid_constant__ GemmParams p)
 {
+    constexpr int STAGES = Cfg::STAGES;
+    constexpr int NCONSUMERS = Cfg::NCONS;       // (shadow the file-scope values of the complex kernel)
+    constexpr int NPRODUCERS = Cfg::NPROD;
+    constexpr int BN = Cfg::BNv;
+    constexpr int SLICE_A = Cfg::SLICE_A, SLICE_B = Cfg::SLICE_B;
+    constexpr int LD_MN_A = Cfg::LD_A, LD_MN_B = Cfg::LD_B;
     extern __shared__ __align__(16) double smem[];
     double* sA = smem;                       // STAGES slices
-    double* sB = smem + STAGES * SLICE;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * STAGES * SLICE);
+    double* sB = smem + STAGES * SLICE_A;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * (SLICE_A + SLICE_B));
     const uint32_t full0 = smem_u32(bars);
     const uint32_t empty0 = smem_u32(bars + STAGES);
 
@@ -233,14 +275,16 @@ dgemm_tiles_kernel(const __grid_constant__ GemmParams p)
     constexpr bool A_KMAJOR = TA;
     constexpr bool B_KMAJOR = !TB;
 
-    Walker<INL> wk;
+    Walker<INL, BM, BN> wk;
     wk.start(p);
     int stage = 0;
     uint32_t phase = 0;
 
     if (warp >= NCONSUMERS) {
         // ------------------------------ producers -----------------------------
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" :: "n"(REGS_PRODUCER));
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" :: "n"(Cfg::REGS_P));
+        if (warp >= NCONSUMERS + NPRODUCERS)
+            return;                  // idle warps: only there to complete the warpgroup
         const int ptid = tid - NCONSUMERS * 32;
 #pragma unroll 1
         while (wk.valid) {
@@ -267,8 +311,8 @@ dgemm_tiles_kernel(const __grid_constant__ GemmParams p)
                         ? it.b + (int64_t)it.n0 * it.ldb + k0
                         : it.b + (int64_t)k0 * it.ldb + it.n0;
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
-                    load_slice<A_KMAJOR>(sA + stage * SLICE, ga, it.lda, it.m, k_rem, it.a16, ptid);
-                    load_slice<B_KMAJOR>(sB + stage * SLICE, gb, it.ldb, it.n, k_rem, it.b16, ptid);
+                    load_slice<A_KMAJOR, BM, LD_MN_A, NPRODUCERS>(sA + stage * SLICE_A, ga, it.lda, it.m, k_rem, it.a16, ptid);
+                    load_slice<B_KMAJOR, BN, LD_MN_B, NPRODUCERS>(sB + stage * SLICE_B, gb, it.ldb, it.n, k_rem, it.b16, ptid);
                     cp_async_mbar_arrive(full0 + 8 * stage);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -280,7 +324,7 @@ dgemm_tiles_kernel(const __grid_constant__ GemmParams p)
     }
 
     // -------------------------------- consumers --------------------------------
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" :: "n"(REGS_CONSUMER));
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" :: "n"(Cfg::REGS_C));
     const int g = lane >> 2;                 // 0..7
     const int t = lane & 3;                  // 0..3
     const int wm = (warp & 1) * 64;          // warp tile origin in the block
@@ -299,8 +343,8 @@ dgemm_tiles_kernel(const __grid_constant__ GemmParams p)
 #pragma unroll 1
         for (int kc = 0; kc < nk; ++kc) {
             mbar_wait(full0 + 8 * stage, phase);
-            const double* a_s = sA + stage * SLICE;
-            const double* b_s = sB + stage * SLICE;
+            const double* a_s = sA + stage * SLICE_A;
+            const double* b_s = sB + stage * SLICE_B;
 #pragma unroll
             for (int k4 = 0; k4 < KC / 4; ++k4) {
                 double af[8], bf[4];
@@ -308,12 +352,12 @@ dgemm_tiles_kernel(const __grid_constant__ GemmParams p)
 #pragma unroll
                 for (int im = 0; im < 8; ++im) {
                     const int x = wm + im * 8 + g;
-                    af[im] = A_KMAJOR ? a_s[x * LD_K + kk] : a_s[kk * LD_MN + x];
+                    af[im] = A_KMAJOR ? a_s[x * LD_K + kk] : a_s[kk * LD_MN_A + x];
                 }
 #pragma unroll
                 for (int in = 0; in < 4; ++in) {
                     const int x = wn + in * 8 + g;
-                    bf[in] = B_KMAJOR ? b_s[x * LD_K + kk] : b_s[kk * LD_MN + x];
+                    bf[in] = B_KMAJOR ? b_s[x * LD_K + kk] : b_s[kk * LD_MN_B + x];
                 }
 #pragma unroll
                 for (int in = 0; in < 4; ++in)
@@ -646,19 +690,19 @@ zgemm_tiles_kernel(const __grid_constant__ ZParams zp)
 }
 
 // ---- host side ----------------------------------------------------------------
-template <bool TA, bool TB, bool INL>
+template <bool TA, bool TB, bool INL, typename Cfg>
 static int launch(int device, cudaStream_t stream, const GemmParams& p)
 {
     static bool configured[64] = {};
-    auto kern = dgemm_tiles_kernel<TA, TB, INL>;
+    auto kern = dgemm_tiles_kernel<TA, TB, INL, Cfg>;
     if (device < 64 && !configured[device]) {
         TE_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           SMEM_BYTES));
+                                           Cfg::SMEM));
         configured[device] = true;
     }
     const int64_t per_wave = (int64_t)p.wave_ctas * p.items_per_cta;
     const int64_t grid = ((p.total_work + per_wave - 1) / per_wave) * p.wave_ctas;
-    kern<<<(unsigned)grid, NTHREADS, SMEM_BYTES, stream>>>(p);
+    kern<<<(unsigned)grid, Cfg::THREADS, Cfg::SMEM, stream>>>(p);
     te::count_launch();
     TE_CUDA_CHECK(cudaGetLastError());
     return TE_OK;
@@ -698,36 +742,73 @@ static int items_per_cta(int device, int64_t total_work)
     return (int)g;
 }
 
-template <bool INL>
+template <bool INL, typename Cfg>
 static int dispatch(int device, cudaStream_t stream, int opa, int opb, const GemmParams& p)
 {
     const bool ta = (opa != TE_OP_N), tb = (opb != TE_OP_N);
-    if (!ta && !tb) return launch<false, false, INL>(device, stream, p);
-    if (!ta &&  tb) return launch<false, true,  INL>(device, stream, p);
-    if ( ta && !tb) return launch<true,  false, INL>(device, stream, p);
-    return launch<true, true, INL>(device, stream, p);
+    if (!ta && !tb) return launch<false, false, INL, Cfg>(device, stream, p);
+    if (!ta &&  tb) return launch<false, true,  INL, Cfg>(device, stream, p);
+    if ( ta && !tb) return launch<true,  false, INL, Cfg>(device, stream, p);
+    return launch<true, true, INL, Cfg>(device, stream, p);
+}
+
+// Which shape the real kernel runs in: 0 wide, 1 pair, 2 pair with a full producer warpgroup
+// (TE_DGEMM_SHAPE=wide|pair|pairfull overrides; see DCfg).
+static int dgemm_shape()
+{
+    static int choice = -1;
+    if (choice < 0) {
+        const char* e = getenv("TE_DGEMM_SHAPE");
+        choice = !e ? 0 : (e[0] == 'w') ? 0 : (strcmp(e, "pairfull") == 0) ? 2 : 1;
+    }
+    return choice;
+}
+
+template <typename Cfg>
+static void shape_params(int device, GemmParams& p, int64_t count, int32_t max_m, int32_t max_n)
+{
+    p.nbm = (max_m + BM - 1) / BM;
+    p.nbn = (max_n + Cfg::BNv - 1) / Cfg::BNv;
+    p.total_work = count * p.nbm * p.nbn;
+    p.wave_ctas = num_sms(device) * Cfg::CTAS_PER_SM;
+    // same time per CTA (about a millisecond at k = 512) whatever the block size
+    p.items_per_cta = items_per_cta(device, p.total_work * Cfg::BNv / BN) * (BN / Cfg::BNv);
+}
+
+template <bool INL>
+static int dgemm_launch_shape(int device, cudaStream_t stream, int opa, int opb, GemmParams& p,
+                              int64_t count, int32_t max_m, int32_t max_n, bool wide)
+{
+    const int shape = wide ? 0 : dgemm_shape();
+    if (shape == 1) {
+        shape_params<CfgPair>(device, p, count, max_m, max_n);
+        return dispatch<INL, CfgPair>(device, stream, opa, opb, p);
+    }
+    if (shape == 2) {
+        shape_params<CfgPairFull>(device, p, count, max_m, max_n);
+        return dispatch<INL, CfgPairFull>(device, stream, opa, opb, p);
+    }
+    shape_params<CfgWide>(device, p, count, max_m, max_n);
+    return dispatch<INL, CfgWide>(device, stream, opa, opb, p);
 }
 
 static bool op_ok(int op) { return op == TE_OP_N || op == TE_OP_T || op == TE_OP_C; }
 
+// `wide`: the call updates op(A) in place (C aliases A) and relies on ONE CTA producing all
+// <= 128 columns of a block row; it must run in the 128-wide shape.
 int dgemm_batched(int device, cudaStream_t stream, int opa, int opb, double alpha, double beta,
-                  const te_tile_desc* desc, int64_t count, int32_t max_m, int32_t max_n)
+                  const te_tile_desc* desc, int64_t count, int32_t max_m, int32_t max_n, bool wide)
 {
     GemmParams p;
     p.desc = desc;
-    p.nbm = (max_m + BM - 1) / BM;
-    p.nbn = (max_n + BN - 1) / BN;
-    p.total_work = count * p.nbm * p.nbn;
-    p.items_per_cta = items_per_cta(device, p.total_work);
-    p.wave_ctas = num_sms(device);
     p.alpha = alpha;
     p.beta = beta;
     p.inline_count = 0;
-    return dispatch<false>(device, stream, opa, opb, p);
+    return dgemm_launch_shape<false>(device, stream, opa, opb, p, count, max_m, max_n, wide);
 }
 
 int dgemm_inline(int device, cudaStream_t stream, int opa, int opb, double alpha, double beta,
-                 const te_tile_desc* desc_host, int count)
+                 const te_tile_desc* desc_host, int count, bool wide)
 {
     GemmParams p;
     p.desc = nullptr;
@@ -737,15 +818,10 @@ int dgemm_inline(int device, cudaStream_t stream, int opa, int opb, double alpha
         if (desc_host[i].m > max_m) max_m = desc_host[i].m;
         if (desc_host[i].n > max_n) max_n = desc_host[i].n;
     }
-    p.nbm = (max_m + BM - 1) / BM;
-    p.nbn = (max_n + BN - 1) / BN;
-    p.total_work = (int64_t)count * p.nbm * p.nbn;
-    p.items_per_cta = items_per_cta(device, p.total_work);
-    p.wave_ctas = num_sms(device);
     p.alpha = alpha;
     p.beta = beta;
     p.inline_count = count;
-    return dispatch<true>(device, stream, opa, opb, p);
+    return dgemm_launch_shape<true>(device, stream, opa, opb, p, count, max_m, max_n, wide);
 }
 
 
@@ -830,13 +906,13 @@ int zgemm_inline(int device, cudaStream_t stream, int opa, int opb, const double
 // dtype dispatch used by the C ABI and by the panel code (te_panel.cu)
 int gemm_batched_any(int device, cudaStream_t stream, int dtype, int opa, int opb,
                      const void* alpha, const void* beta, const te_tile_desc* desc,
-                     int64_t count, int32_t max_m, int32_t max_n)
+                     int64_t count, int32_t max_m, int32_t max_n, bool inplace_a)
 {
     if (count == 0 || max_m == 0 || max_n == 0)
         return TE_OK;
     if (dtype == TE_F64)
         return dgemm_batched(device, stream, opa, opb, *(const double*)alpha,
-                             *(const double*)beta, desc, count, max_m, max_n);
+                             *(const double*)beta, desc, count, max_m, max_n, inplace_a);
     if (dtype == TE_C64)
         return zgemm_batched(device, stream, opa, opb, (const double*)alpha, (const double*)beta,
                              desc, count, max_m, max_n);
@@ -844,13 +920,14 @@ int gemm_batched_any(int device, cudaStream_t stream, int dtype, int opa, int op
 }
 
 int gemm_inline_any(int device, cudaStream_t stream, int dtype, int opa, int opb,
-                    const void* alpha, const void* beta, const te_tile_desc* desc_host, int count)
+                    const void* alpha, const void* beta, const te_tile_desc* desc_host, int count,
+                    bool inplace_a)
 {
     if (count == 0)
         return TE_OK;
     if (dtype == TE_F64)
         return dgemm_inline(device, stream, opa, opb, *(const double*)alpha,
-                            *(const double*)beta, desc_host, count);
+                            *(const double*)beta, desc_host, count, inplace_a);
     if (dtype == TE_C64)
         return zgemm_inline(device, stream, opa, opb, (const double*)alpha, (const double*)beta,
                             desc_host, count);
@@ -870,7 +947,7 @@ extern "C" int te_gemm_batched(int device, void* stream, int dtype, int opa, int
     int st = te::set_device(device);
     if (st != TE_OK) return st;
     return te::gemm_batched_any(device, (cudaStream_t)stream, dtype, opa, opb, alpha, beta, desc,
-                                count, max_m, max_n);
+                                count, max_m, max_n, false);
 }
 
 extern "C" int te_gemm_inline(int device, void* stream, int dtype, int opa, int opb,
@@ -883,5 +960,5 @@ extern "C" int te_gemm_inline(int device, void* stream, int dtype, int opa, int 
     int st = te::set_device(device);
     if (st != TE_OK) return st;
     return te::gemm_inline_any(device, (cudaStream_t)stream, dtype, opa, opb, alpha, beta,
-                               desc_host, count);
+                               desc_host, count, false);
 }

@@ -23,11 +23,14 @@
 namespace te {
 
 // implemented in te_gemm.cu
+// inplace_a: C aliases op(A) (X <- X * M with n <= 128): one CTA must own whole block rows,
+// so the real kernel is run in its 128-column shape (te_gemm.cu, DCfg)
 int gemm_batched_any(int device, cudaStream_t stream, int dtype, int opa, int opb,
                      const void* alpha, const void* beta, const te_tile_desc* desc,
-                     int64_t count, int32_t max_m, int32_t max_n);
+                     int64_t count, int32_t max_m, int32_t max_n, bool inplace_a = false);
 int gemm_inline_any(int device, cudaStream_t stream, int dtype, int opa, int opb,
-                    const void* alpha, const void* beta, const te_tile_desc* desc_host, int count);
+                    const void* alpha, const void* beta, const te_tile_desc* desc_host, int count,
+                    bool inplace_a = false);
 
 constexpr int PANEL_THREADS = 512;
 
@@ -307,7 +310,7 @@ static int potrf_tile(int device, cudaStream_t stream, int dtype, int uplo, int 
             // P <- P * inv(L)^H   (in place: the CTA tile spans all ib columns)
             d.a = P; d.b = scratch; d.c = P; d.m = rem; d.n = ib; d.k = ib;
             d.lda = lda; d.ldb = IB; d.ldc = lda; d.flags = TE_TILE_GENERAL;
-            st = gemm_inline_any(device, stream, dtype, TE_OP_N, TE_OP_C, one, zero, &d, 1);
+            st = gemm_inline_any(device, stream, dtype, TE_OP_N, TE_OP_C, one, zero, &d, 1, true);
             if (st != TE_OK) return st;
             // A22 <- A22 - P P^H on the lower triangle
             d.a = P; d.b = P; d.c = A22; d.m = rem; d.n = rem; d.k = ib;
@@ -452,9 +455,11 @@ static int trsm_batched(int device, cudaStream_t stream, int dtype, int side, in
                                   upd + (size_t)s * count, count, mm, nn);
             if (st != TE_OK) return st;
         }
+        // in place: X(:, blk) <- T * inv (right: C aliases A), X(blk, :) <- inv * T (left: C
+        // aliases B, safe in any shape because a CTA reads only its own columns of B)
         st = gemm_batched_any(device, stream, dtype, p.right ? TE_OP_N : opa,
                               p.right ? opa : TE_OP_N, (s == 0) ? alpha : (const void*)one, zero,
-                              mul + (size_t)s * count, count, mm, nn);
+                              mul + (size_t)s * count, count, mm, nn, p.right != 0);
         if (st != TE_OK) return st;
     }
     return TE_OK;
@@ -571,7 +576,7 @@ static int getrf_nopiv_tile(int device, cudaStream_t stream, int dtype, int m, i
             // L21 <- A21 inv(U11)   (in place: a CTA tile spans all ib columns)
             d.a = A21; d.b = invU; d.c = A21; d.m = rem_m; d.n = ib; d.k = ib;
             d.lda = lda; d.ldb = IB; d.ldc = lda;
-            st = gemm_inline_any(device, stream, dtype, TE_OP_N, TE_OP_N, one, zero, &d, 1);
+            st = gemm_inline_any(device, stream, dtype, TE_OP_N, TE_OP_N, one, zero, &d, 1, true);
             if (st != TE_OK) return st;
         }
         if (rem_n > 0) {
