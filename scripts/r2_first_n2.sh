@@ -11,4 +11,6 @@ SLATE_B200_BCAST=coalesce timeout 900 $TR --master-port 29604 scripts/mp_parity.
 for plane in peer nccl coalesce; do
   SLATE_B200_BCAST=$plane timeout 600 $TR --master-port 29605 bench.py --gpus 2 --steps 16 --warmup 3 --no-e2e --no-cpu --potrf-n 49152 > gpurun_out/r2_bench_n2_$plane.log 2>&1; echo "bench $plane rc=$?"
 done
+timeout 600 python -m pytest tests/test_gpu_ref_binding.py -x -q > gpurun_out/r2_pytest_ref_binding_2dev.log 2>&1; echo "ref_binding, one process x 2 devices rc=$?"; tail -n 3 gpurun_out/r2_pytest_ref_binding_2dev.log
+timeout 600 python scripts/ref_binding_bench.py 16384 24576 512 > gpurun_out/r2_ref_binding_bench_2dev.json 2>/dev/null; cat gpurun_out/r2_ref_binding_bench_2dev.json
 tail -n 3 gpurun_out/r2_peerbench_n2.log gpurun_out/r2_parity_peer_n2.log gpurun_out/r2_parity_coalesce_n2.log

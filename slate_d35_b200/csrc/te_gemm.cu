@@ -47,16 +47,22 @@ constexpr int REGS_PRODUCER = 56;                  // setmaxnreg budgets: 56*P +
 constexpr int REGS_CONSUMER = 224;                 //   for C = 2P consumer / producer threads
 constexpr int LD_K = KC + 4;             // row stride (doubles) of an [mn][k] slice
 
-// Shape of the real kernel.  Three are built:
-//   Wide      128x128 CTA tile, 8 consumer + 4 producer warps, 5-stage ring, ONE CTA per SM;
-//   Pair      128x64  CTA tile, 4 consumer + 2 producer warps, 3-stage ring, TWO CTAs per SM;
-//   PairFull  as Pair, with two idle warps completing the producer warpgroup (below).
-// The warp tile (64x32, 128 accumulator registers) and the DMMA / LDS mix are the same.  With
-// one CTA per SM all eight consumer warps reach the epilogue of a block together and the tensor
-// pipe idles while C is read, scaled and written (ncu: pipe active 88.5 %, long-scoreboard
-// stalls 21 %); two independent CTAs per SM drift apart, so one CTA's epilogue, pipeline refill
-// and work-item decode run under the other's DMMA stream.  The price is 1.5x the L2 -> shared
-// traffic per flop (A slice per 64 columns instead of 128), far below what L2 delivers.
+// Shape of the real kernel.  Two are built:
+//   Wide      128x128 CTA tile, 8 consumer + 4 producer warps, 5-stage ring, ONE CTA per SM
+//             (the default, and the shape every in-place panel GEMM needs);
+//   PairFull  128x64 CTA tile, 4 consumer + 2 producer warps (+ 2 idle warps that complete the
+//             producer warpgroup), 3-stage ring, TWO CTAs per SM.  TE_DGEMM_SHAPE=pairfull.
+// The warp tile (64x32, 128 accumulator registers) and the DMMA / LDS mix are the same.  The idea
+// of the second shape: with one CTA per SM all eight consumer warps reach the epilogue of a block
+// together and the tensor pipe idles while C is read, scaled and written (ncu: pipe active
+// 88.5 %, long-scoreboard stalls 21 %); two independent CTAs per SM drift apart, so one CTA's
+// epilogue runs under the other's DMMA stream.  MEASURED (round 2, one B200, n = 65536): it is
+// SLOWER, 30.8 against 32.7 TFLOP/s over 8 block steps (29.6 against 31.6 at the 2x4 grid's launch
+// shape): 128 registers per thread at launch leave the consumers 200 instead of 224 (3x the
+// spill traffic), the ring is 3 deep instead of 5, and A slices cross L2 -> shared 1.5x as
+// often.  Kept selectable as the record of that experiment.  (A 192-thread variant whose
+// producer "warpgroup" had only two warps hung in setmaxnreg: the instruction is specified per
+// group of four warps.)
 template <int BN_, int NCONS_, int NPROD_, int STAGES_, int CTAS_PER_SM_, int NIDLE_ = 0,
           int REGS_C_ = REGS_CONSUMER, int REGS_P_ = REGS_PRODUCER>
 struct DCfg {
@@ -80,8 +86,6 @@ struct DCfg {
                   "setmaxnreg budget");
 };
 using CfgWide = DCfg<128, 8, 4, 5, 1>;
-// Pair: the producer "warpgroup" has two warps only (192 threads per CTA).
-using CfgPair = DCfg<64, 4, 2, 3, 2>;
 // PairFull: two idle warps complete the producer warpgroup (setmaxnreg is specified per
 // warpgroup of four warps); they give their registers back and exit.  256 threads per CTA,
 // 128 registers per thread at launch, so the consumers get 200 instead of 224.
@@ -752,14 +756,14 @@ static int dispatch(int device, cudaStream_t stream, int opa, int opb, const Gem
     return launch<true, true, INL, Cfg>(device, stream, p);
 }
 
-// Which shape the real kernel runs in: 0 wide, 1 pair, 2 pair with a full producer warpgroup
-// (TE_DGEMM_SHAPE=wide|pair|pairfull overrides; see DCfg).
+// Which shape the real kernel runs in: 0 wide (default), 2 two CTAs per SM
+// (TE_DGEMM_SHAPE=wide|pairfull; see DCfg).
 static int dgemm_shape()
 {
     static int choice = -1;
     if (choice < 0) {
         const char* e = getenv("TE_DGEMM_SHAPE");
-        choice = !e ? 0 : (e[0] == 'w') ? 0 : (strcmp(e, "pairfull") == 0) ? 2 : 1;
+        choice = (e && strcmp(e, "pairfull") == 0) ? 2 : 0;
     }
     return choice;
 }
@@ -780,10 +784,6 @@ static int dgemm_launch_shape(int device, cudaStream_t stream, int opa, int opb,
                               int64_t count, int32_t max_m, int32_t max_n, bool wide)
 {
     const int shape = wide ? 0 : dgemm_shape();
-    if (shape == 1) {
-        shape_params<CfgPair>(device, p, count, max_m, max_n);
-        return dispatch<INL, CfgPair>(device, stream, opa, opb, p);
-    }
     if (shape == 2) {
         shape_params<CfgPairFull>(device, p, count, max_m, max_n);
         return dispatch<INL, CfgPairFull>(device, stream, opa, opb, p);
