@@ -64,18 +64,25 @@ def main():
                 H = sl.HermitianMatrix(uplo, n, nb, p, q).generate(7, dominant=True)
                 info = sl.potrf(H, lookahead=la)
                 got = assemble(H)
+                berr_dev = None
                 if uplo == "L":
+                    # the engine's own distributed residual (what bench.py uses at full size)
                     r, a0 = sl.potrf_residual(H, 7, True)
                     t = torch.tensor([r, a0], dtype=torch.float64, device="cuda")
                     dist.all_reduce(t)
-                    berr = float(t[0].sqrt() / (n * t[1].sqrt()))
-                else:
-                    berr = 0.0
+                    berr_dev = float(t[0].sqrt() / (n * t[1].sqrt()))
                 if rank == 0:
                     want = ol.matgen(7, n, n)
                     want[np.arange(n), np.arange(n)] += n
-                    assert ol.oracle().oracle_dpotrf(ord(uplo), n, nb, ol.P(want), n) == 0
                     tri = np.tril if uplo == "L" else np.triu
+                    # dense backward error of the assembled factor, both triangles
+                    S = tri(want) + tri(want, -1 if uplo == "L" else 1).T
+                    F = tri(got)
+                    R = (F @ F.T if uplo == "L" else F.T @ F) - S
+                    berr = float(np.linalg.norm(R) / (n * np.linalg.norm(S)))
+                    if berr_dev is not None:
+                        berr = max(berr, berr_dev)
+                    assert ol.oracle().oracle_dpotrf(ord(uplo), n, nb, ol.P(want), n) == 0
                     err = np.abs(tri(got) - tri(want)).max() / np.abs(tri(want)).max()
                     ok = info == 0 and err <= 50 * EPS and berr <= 50 * EPS
                     fails += (not ok)
@@ -167,9 +174,8 @@ def main():
 
     # hemm / symm, her2k and getrf_nopiv on the grids (their broadcast plans run over gloo in
     # tests/mp_worker.py and are replayed on 2x2 / 2x4 in tests/test_plans_grid.py; this is the
-    # same on GPUs over NCCL).  Written after the round's multi-GPU budget was spent, so NOT YET
-    # RUN on several GPUs: opt in with MP_PARITY_EXTRA=1 until it has been.
-    for (p, q) in (GRIDS[world] if os.environ.get("MP_PARITY_EXTRA") == "1" else []):
+    # same on GPUs).  MP_PARITY_EXTRA=0 skips it.
+    for (p, q) in (GRIDS[world] if os.environ.get("MP_PARITY_EXTRA", "1") == "1" else []):
         n, nrhs, nb = 1500, 700, 256
         S0 = ol.matgen(30, n, n)
         S0 = (S0 + S0.T) / 2

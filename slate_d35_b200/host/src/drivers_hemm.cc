@@ -128,11 +128,20 @@ void hemm_symm(bool hermitian, Side side, scalar_t alpha, AMatrix A, Matrix<scal
             internal::symm<Target::Devices>(Side::Left, alpha, A.sub(k, k), std::move(B_row), bet,
                                             C.sub(k, k, 0, nt - 1), 0, queue_0);
 
-        // drop what this step received
+        // drop what this step received.  A stored tile (a, b) travels twice -- in step b as
+        // A(a, b) to the owners of block row a of C and in step a, transposed, as A(b, a) to the
+        // owners of block row b -- so a rank gives back only the copy it was a destination of in
+        // THIS step (it owns part of block row i of C); otherwise, with lookahead, it would drop
+        // the copy a later step has already delivered (seen on a 2 x 1 grid).
         for (int64_t i = 0; i < mt; ++i) {
             const bool direct = (i == k) || stored(i, k);
             const int64_t ti = direct ? i : k, tj = direct ? k : i;
-            if (!A.tileIsLocal(ti, tj)) A.releaseRemoteWorkspaceTile(ti, tj);
+            if (!A.tileIsLocal(ti, tj)) {
+                bool destination = false;
+                for (int64_t j = 0; j < nt && !destination; ++j)
+                    destination = C.tileIsLocal(i, j);
+                if (destination) A.releaseRemoteWorkspaceTile(ti, tj);
+            }
             else A.releaseLocalWorkspaceTile(ti, tj);
         }
         A.storage()->flushErased();
