@@ -567,7 +567,7 @@ protected:
     void finishHostCopies()
     {
         if (host_copies_pending_) {
-            Engine::instance().sync_comm();
+            Engine::instance().sync_home();
             host_copies_pending_ = false;
         }
     }
@@ -608,14 +608,16 @@ void BaseMatrix<scalar_t>::tileGet(int64_t i, int64_t j, int device, bool modify
             // host instances are ColMajor: bring the device array back first (comm stream)
             if (node.dev->layout() != Layout::ColMajor)
                 tileLayoutConvert(i, j, 0, Layout::ColMajor, -1);
-            // device -> host: after the launch that produced the data
-            eng.comm_wait_queue_seq(node.write_queue, node.write_seq);
+            // device -> host, on the home stream: after the launch that produced the data and
+            // after the comm-stream work (broadcast, layout conversion) that filled the tile
+            eng.home_wait_queue_seq(node.write_queue, node.write_seq);
+            eng.home_wait_comm_seq(node.comm_seq);
             Tile<scalar_t>* s = node.dev;
             Tile<scalar_t>* d = node.host;
             slate_te_call(te_memcpy2d_async(d->data(), sizeof(scalar_t) * d->stride(), s->data(),
                                             sizeof(scalar_t) * s->stride(),
                                             sizeof(scalar_t) * s->mb(), s->nb(), TE_COPY_D2H,
-                                            eng.comm_stream()));
+                                            eng.home_stream()));
             host_copies_pending_ = true;
             node.host_state = MOSI::Shared;
             if (node.dev_state == MOSI::Modified) node.dev_state = MOSI::Shared;

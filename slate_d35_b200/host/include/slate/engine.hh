@@ -94,6 +94,11 @@ public:
     int num_devices() const { return te_device_count() > 0 ? 1 : 0; }
 
     void* comm_stream();
+    /// Stream of the device-to-host copies that bring tiles home (tileGet on HostNum).  Separate
+    /// from the comm stream: a write-back waits for the launch that produced its tile, and on the
+    /// comm stream that wait would hold up every host-to-device prefetch and broadcast queued
+    /// behind it (PCIe is full duplex; the two directions have nothing to wait for in each other).
+    void* home_stream();
     void* compute_stream(int queue);
     static const int MaxQueues = 16;
 
@@ -105,6 +110,10 @@ public:
     uint64_t next_queue_seq(int q) const { return queue_seq_[q] + 1; }
     void queue_wait_queue_seq(int q, int other, uint64_t seq);
     void comm_wait_queue_seq(int other, uint64_t seq);
+    /// the home stream behind mark `seq` of compute queue `other` / mark `seq` of the comm stream
+    void home_wait_queue_seq(int other, uint64_t seq);
+    void home_wait_comm_seq(uint64_t seq);
+    void sync_home();
     /// Records a point on the comm stream and returns its sequence number; tiles filled by
     /// the comm work enqueued before it carry that number (TileNode::comm_seq).
     uint64_t mark_comm();
@@ -192,6 +201,8 @@ private:
     bool initialized_ = false;
     int device_ = 0;
     void* comm_stream_ = nullptr;
+    void* home_stream_ = nullptr;
+    bool home_used_ = false;
     void* comm_event_ = nullptr;
     uint64_t comm_seq_ = 0;
     static const int QueueRing = 64;

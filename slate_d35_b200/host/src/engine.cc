@@ -116,6 +116,7 @@ void Engine::initialize(int device)
     if (te_device_count() == 0)
         return;     // host-only process: matrices can exist, device paths throw
     slate_te_call(te_stream_create(device_, 1, &comm_stream_));
+    slate_te_call(te_stream_create(device_, 1, &home_stream_));
     slate_te_call(te_event_create(device_, 0, &comm_event_));
     void* p = nullptr;
     slate_te_call(te_device_malloc(device_, sizeof(int) * (size_t)(info_cap_ + 1), &p));
@@ -126,6 +127,35 @@ void* Engine::comm_stream()
 {
     slate_assert(comm_stream_ != nullptr);
     return comm_stream_;
+}
+
+void* Engine::home_stream()
+{
+    slate_assert(home_stream_ != nullptr);
+    home_used_ = true;
+    return home_stream_;
+}
+
+void Engine::home_wait_queue_seq(int other, uint64_t seq)
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    if (other < 0 || !queue_[other] || seq == 0) return;
+    slate_te_call(te_stream_wait_event(home_stream(), queue_mark_event(other, seq)));
+}
+
+void Engine::home_wait_comm_seq(uint64_t seq)
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    if (seq == 0) return;
+    if (seq > comm_seq_) mark_comm();
+    const int slot = (int)(seq % CommRing);
+    slate_te_call(te_stream_wait_event(home_stream(),
+                                       comm_ring_seq_[slot] == seq ? comm_ring_event_[slot] : comm_event_));
+}
+
+void Engine::sync_home()
+{
+    if (home_stream_ && home_used_) slate_te_call(te_stream_sync(device_, home_stream_));
 }
 
 void* Engine::compute_stream(int q)
@@ -399,6 +429,11 @@ void Engine::defer(unsigned queue_mask, bool comm, std::function<void()> fn)
         void* e = new_event();
         slate_te_call(te_event_record(e, comm_stream_));
         d.events.push_back(e);
+        if (home_used_) {            // a tile still being copied home must not be recycled either
+            e = new_event();
+            slate_te_call(te_event_record(e, home_stream_));
+            d.events.push_back(e);
+        }
     }
     if (d.events.empty()) {
         d.fn();
@@ -447,6 +482,7 @@ void* Engine::timer_begin()
     for (int q = 1; q < MaxQueues; ++q)
         if (queue_[q]) slate_te_call(te_stream_wait_event(queue_[q], e));
     slate_te_call(te_stream_wait_event(comm_stream(), e));
+    slate_te_call(te_stream_wait_event(home_stream_, e));
     return e;
 }
 
@@ -461,9 +497,9 @@ float Engine::timer_end(void* start)
             recycle_event(e);
         }
     }
-    {
+    for (void* side : {comm_stream(), home_stream_}) {
         void* e = new_event();
-        slate_te_call(te_event_record(e, comm_stream()));
+        slate_te_call(te_event_record(e, side));
         slate_te_call(te_stream_wait_event(s0, e));
         recycle_event(e);
     }
