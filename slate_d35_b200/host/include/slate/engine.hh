@@ -209,14 +209,17 @@ private:
     void* queue_ring_event_[MaxQueues][QueueRing] = {};
     uint64_t queue_ring_seq_[MaxQueues][QueueRing] = {};
     void* queue_mark_event(int other, uint64_t seq);
-    static const int CommRing = 64;
+    static const int CommRing = 256;
     void* comm_ring_event_[CommRing] = {};
     uint64_t comm_ring_seq_[CommRing] = {};
     void* queue_[MaxQueues] = {};
     void* queue_event_[MaxQueues] = {};
     uint64_t queue_seq_[MaxQueues] = {};
     uint64_t queue_saw_comm_[MaxQueues] = {};
-    static const int RingDepth = 4;
+    // descriptor slots per queue = launches the host may run ahead of the device.  16: a burst of
+    // host work (enqueueing the 2 x 2048 tile copies of a slab of host-origin C takes ~45 ms) must
+    // not drain the device's queue (measured: with 4 slots the update idled 45 ms per slab)
+    static const int RingDepth = 16;
     DescSlot ring_[MaxQueues][RingDepth];
     int ring_next_[MaxQueues] = {};
     void* scratch_[MaxQueues] = {};

@@ -108,9 +108,22 @@ void gemmC(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t be
         ~BulkTrafficGuard() { Engine::instance().set_bulk_host_traffic(false); }
     } bulk_guard(A.origin() != Target::Devices || B.origin() != Target::Devices
                  || C.origin() != Target::Devices);
+    // the first and the last slab are half as wide as the others: the first one's transfer
+    // is the start-up time nothing can hide, the last one's write-back is the tail
+    std::vector<int64_t> slab_begin(nslab + 1, 0);
+    {
+        const bool weighted = nslab > 2 && C.nt() >= 4 * nslab;         // weights 1, 2, ..., 2, 1
+        const int64_t units = weighted ? 2 * nslab - 2 : nslab;
+        int64_t acc = 0;
+        for (int64_t s = 0; s < nslab; ++s) {
+            slab_begin[s] = acc * C.nt() / units;
+            acc += (weighted && s > 0 && s < nslab - 1) ? 2 : 1;
+        }
+        slab_begin[nslab] = C.nt();
+    }
     auto slab_cols = [&](int64_t s, int64_t* j1, int64_t* j2) {
-        *j1 = s * C.nt() / nslab;
-        *j2 = (s + 1) * C.nt() / nslab - 1;
+        *j1 = slab_begin[s];
+        *j2 = slab_begin[s + 1] - 1;
     };
     int64_t skew = 0;
     if (nslab > 1) {
@@ -145,20 +158,31 @@ void gemmC(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t be
         BcastListTag list_B = gemm_bcast_list(1, A, B, C, k);
         B.template listBcastMT<Target::Devices>(list_B, layout);
     };
-    // fetch_C (src/gemmC.cc:70-74), one slab; the consuming launch waits for its own tiles
-    int64_t next_fetch = 0;
-    auto fetch_slabs_upto = [&](int64_t s_last) {
-        for (; next_fetch <= s_last && next_fetch < nslab; ++next_fetch) {
-            int64_t j1, j2;
-            slab_cols(next_fetch, &j1, &j2);
-            C.sub(0, C.mt() - 1, j1, j2).tileGetAllForWritingOnDevices(LayoutConvert(layout), -1);
-        }
+    // fetch_C (src/gemmC.cc:70-74), by block columns; the consuming launch waits for its own
+    // tiles.  Slab s is first used in iteration skew * s; its columns are asked for a few per
+    // iteration during the slab period before that, so that neither the copy engine (panels
+    // queue behind them) nor the host (2048 copies take ~40 ms to enqueue) sees a burst.
+    int64_t next_col = 0;
+    auto fetch_cols_upto = [&](int64_t j_end) {        // columns [next_col, j_end)
+        j_end = std::min<int64_t>(j_end, C.nt());
+        if (j_end <= next_col) return;
+        C.sub(0, C.mt() - 1, next_col, j_end - 1).tileGetAllForWritingOnDevices(LayoutConvert(layout), -1);
+        next_col = j_end;
+    };
+    auto fetch_for_iteration = [&](int64_t t) {
+        if (nslab == 1) return;
+        const int64_t s = t / skew + 1;                  // the slab being prefetched
+        if (s >= nslab) { fetch_cols_upto(C.nt()); return; }
+        const int64_t r = t % skew;                       // complete one iteration early
+        const int64_t parts = std::max<int64_t>(1, skew - 1);
+        const int64_t width = slab_begin[s + 1] - slab_begin[s];
+        fetch_cols_upto(slab_begin[s] + std::min<int64_t>(width, (width * (r + 1) + parts - 1) / parts));
     };
 
     HostTimer ht;
     ht.start();
     bcast(0);
-    fetch_slabs_upto(nslab > 1 ? 1 : 0);
+    fetch_cols_upto(slab_begin[1]);                       // slab 0 (all of C when nslab == 1)
     for (int64_t k = 1; k <= lookahead && k < kt; ++k)
         bcast(k);
     ht.stop(0);
@@ -168,9 +192,7 @@ void gemmC(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t be
         ht.start();
         if (t > 0 && t + lookahead < kt)
             bcast(t + lookahead);
-        // slab s is first used in iteration skew * s: ask for it one slab period earlier
-        if (nslab > 1)
-            fetch_slabs_upto(t / skew + 1);
+        fetch_for_iteration(t);
         ht.stop(0);
         ht.start();
 
