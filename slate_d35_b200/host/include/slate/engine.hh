@@ -108,6 +108,8 @@ public:
     /// sequence number the NEXT mark_queue(q) will carry: a tile written by the launch being
     /// prepared remembers (q, that number) and later consumers wait for exactly that mark
     uint64_t next_queue_seq(int q) const { return queue_seq_[q] + 1; }
+    /// true once mark `seq` of queue q has been reached on the device (never blocks)
+    bool queue_mark_done(int q, uint64_t seq);
     void queue_wait_queue_seq(int q, int other, uint64_t seq);
     void comm_wait_queue_seq(int other, uint64_t seq);
     /// the home stream behind mark `seq` of compute queue `other` / mark `seq` of the comm stream

@@ -9,6 +9,8 @@
 // from which queue last wrote each tile (BaseMatrix::tileGet), and broadcast workspace is
 // recycled by deferred release.  Lookahead keeps its meaning: how many block columns the
 // broadcasts / panel factorisations run ahead of the trailing update.
+#include <deque>
+#include <thread>
 #include "slate/slate.hh"
 
 #include <chrono>
@@ -179,6 +181,27 @@ void gemmC(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t be
         fetch_cols_upto(slab_begin[s] + std::min<int64_t>(width, (width * (r + 1) + parts - 1) / parts));
     };
 
+    // Write-back of finished slabs.  Its device-to-host copies wait (on the home stream) for the
+    // slab's last launch, which the host has enqueued several launches ahead of the device; a
+    // stream that is blocked on an event accepts only ~1000 more operations before the ENQUEUE
+    // blocks the host (measured: the host then sat until the device had caught up, the device
+    // queue ran dry and every slab cost 57 ms of idle GPU).  So a finished slab is queued here
+    // and its copies are enqueued, a few block columns per iteration, once that launch is done.
+    struct Writeback { int64_t j_next, j_end; uint64_t seq; };
+    std::deque<Writeback> writebacks;
+    auto drain_writebacks = [&](int64_t max_cols) {
+        Engine& eng = Engine::instance();
+        while (!writebacks.empty() && max_cols > 0) {
+            Writeback& w = writebacks.front();
+            if (!eng.queue_mark_done(queue_0, w.seq)) break;
+            const int64_t j2 = std::min<int64_t>(w.j_end, w.j_next + max_cols);
+            C.sub(0, C.mt() - 1, w.j_next, j2 - 1).tileUpdateAllOriginAsync();
+            max_cols -= j2 - w.j_next;
+            w.j_next = j2;
+            if (w.j_next >= w.j_end) writebacks.pop_front();
+        }
+    };
+
     HostTimer ht;
     ht.start();
     bcast(0);
@@ -217,14 +240,16 @@ void gemmC(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t be
                                  queue_0);
             internal::gemm_multi(internal::TargetType<Target::Devices>(), alpha, rest, one, layout,
                                  queue_0);
-            // a slab that has just had its last update goes home behind that launch
+            // a slab that has just had its last update goes home once that launch is done
             for (int64_t s = 0; s < nslab; ++s) {
                 if (t - skew * s == kt - 1) {
                     int64_t j1, j2;
                     slab_cols(s, &j1, &j2);
-                    C.sub(0, C.mt() - 1, j1, j2).tileUpdateAllOriginAsync();
+                    if (j2 >= j1)
+                        writebacks.push_back({j1, j2 + 1, Engine::instance().next_queue_seq(queue_0) - 1});
                 }
             }
+            drain_writebacks(std::max<int64_t>(2, C.nt() / 16));
         }
         ht.stop(1);
         ht.start();
@@ -246,6 +271,11 @@ void gemmC(scalar_t alpha, Matrix<scalar_t>& A, Matrix<scalar_t>& B, scalar_t be
 
     // src/gemmC.cc:187-190
     ht.start();
+    // slabs still waiting to go home: each as soon as its last launch has finished
+    while (!writebacks.empty()) {
+        drain_writebacks(C.nt());
+        if (!writebacks.empty()) std::this_thread::sleep_for(std::chrono::microseconds(100));
+    }
     C.tileUpdateAllOrigin();
     C.releaseWorkspace();
     Engine::instance().sync_all();

@@ -202,6 +202,17 @@ void* Engine::queue_mark_event(int other, uint64_t seq)
     return queue_event_[other];
 }
 
+bool Engine::queue_mark_done(int q, uint64_t seq)
+{
+    std::lock_guard<std::recursive_mutex> lock(mu_);
+    if (q < 0 || !queue_[q] || seq == 0) return true;
+    if (seq > queue_seq_[q]) return false;                   // not even marked yet
+    const int slot = (int)(seq % QueueRing);
+    if (queue_ring_seq_[q][slot] != seq)
+        return true;    // left the ring: >= QueueRing marks ago, and the host is never that far ahead
+    return te_event_query_done(queue_ring_event_[q][slot]) == 1;
+}
+
 void Engine::queue_wait_queue_seq(int q, int other, uint64_t seq)
 {
     std::lock_guard<std::recursive_mutex> lock(mu_);
