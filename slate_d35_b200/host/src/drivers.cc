@@ -382,7 +382,10 @@ int64_t potrf(HermitianMatrix<scalar_t>& A_in, Options const& opts)
             auto panel = A.sub(k, A_nt - 1, k, k);
             panel.releaseRemoteWorkspace();
             if (A.origin() != Target::Devices) {
-                panel.tileUpdateAllOrigin();
+                // enqueued behind the panel's last writer on the home stream; the host does not
+                // wait per step (the final tileUpdateAllOrigin / sync_all completes the copies,
+                // and the device blocks go back to the pool only when they have been read)
+                panel.tileUpdateAllOriginAsync();
                 panel.releaseLocalWorkspace();
             }
         }

@@ -119,9 +119,9 @@ int64_t getrf_nopiv(Matrix<scalar_t>& A, Options const& opts)
             col.releaseRemoteWorkspace();
             row.releaseRemoteWorkspace();
             if (A.origin() != Target::Devices) {
-                col.tileUpdateAllOrigin();
+                col.tileUpdateAllOriginAsync();
                 col.releaseLocalWorkspace();
-                row.tileUpdateAllOrigin();
+                row.tileUpdateAllOriginAsync();
                 row.releaseLocalWorkspace();
             }
         }
