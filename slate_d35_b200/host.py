@@ -33,6 +33,10 @@ def hostlib():
     L.sb_initialize.argtypes = [C.c_int, C.c_int, C.c_int, vp]
     L.sb_matrix_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, i64, i64, i64, C.c_int,
                                    C.c_int, C.c_int, vp, i64, C.POINTER(vp)]
+    L.sb_matrix_create_tiled.argtypes = [C.c_int, C.c_int, C.c_int, i64, i64, C.POINTER(i64), i64,
+                                         C.POINTER(i64), i64, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
+    L.sb_matrix_from_devices.argtypes = [C.c_int, C.c_int, C.c_int, i64, i64, vp, i64, i64, C.c_int,
+                                         C.c_int, C.POINTER(vp)]
     L.sb_matrix_destroy.argtypes = [vp]
     L.sb_matrix_generate.argtypes = [vp, i64, C.c_int, C.c_int]
     L.sb_matrix_to_host.argtypes = [vp, vp, i64]
@@ -197,8 +201,48 @@ class _Base:
         return a.value, c.value
 
 
+def _adopt(cls, h, m, n, nb, p, q, dtype, uplo="L", keep=None):
+    """wrap a handle made by one of the alternative constructors"""
+    self = cls.__new__(cls)
+    self.m, self.n, self.nb, self.p, self.q = m, n, nb, p, q
+    self.dtype = np.dtype(dtype)
+    self.uplo = uplo
+    self._host_array = keep            # keeps the caller's (device) memory alive
+    self.h = h
+    return self
+
+
+def _sizes(v):
+    return (i64 * len(v))(*[int(x) for x in v])
+
+
 class Matrix(_Base):
     kind = GENERAL
+
+    @classmethod
+    def tiled(cls, row_sizes, col_sizes, p=1, q=1, dtype=np.float64, origin="D"):
+        """Lambda constructor (include/slate/Matrix.hh:33-38): tile (i, j) is row_sizes[i] x
+        col_sizes[j]; sizes need not be uniform.  Owners 2D block-cyclic over p x q."""
+        if not _initialized:
+            initialize()
+        m, n = int(sum(row_sizes)), int(sum(col_sizes))
+        h = vp()
+        _check(hostlib().sb_matrix_create_tiled(_dtype_code(dtype), GENERAL, ord("L"), m, n, _sizes(row_sizes),
+                                                len(row_sizes), _sizes(col_sizes), len(col_sizes), p, q,
+                                                ord(origin), C.byref(h)))
+        return _adopt(cls, h, m, n, max(max(row_sizes), max(col_sizes)), p, q, dtype)
+
+    @classmethod
+    def fromDevices(cls, m, n, dev_tensor, lda, nb, p=1, q=1, dtype=np.float64):
+        """Matrix::fromDevices (include/slate/Matrix.hh:102-112): tiles are views into the caller's
+        device array (a torch CUDA tensor holding this rank's local matrix, column major, leading
+        dimension lda); results land in that memory."""
+        if not _initialized:
+            initialize()
+        h = vp()
+        _check(hostlib().sb_matrix_from_devices(_dtype_code(dtype), GENERAL, ord("L"), m, n,
+                                                dev_tensor.data_ptr(), lda, nb, p, q, C.byref(h)))
+        return _adopt(cls, h, m, n, nb, p, q, dtype, keep=dev_tensor)
 
     @classmethod
     def fromLAPACK(cls, a, nb, p=1, q=1, m=None):
@@ -223,6 +267,26 @@ class HermitianMatrix(_Base):
     @classmethod
     def fromLAPACK(cls, uplo, a, nb, p=1, q=1):
         return cls(uplo, a.shape[0], nb, p, q, a.dtype, origin="H", host_array=a)
+
+    @classmethod
+    def tiled(cls, uplo, sizes, p=1, q=1, dtype=np.float64, origin="D"):
+        """Lambda constructor: square, tile (i, j) is sizes[i] x sizes[j]."""
+        if not _initialized:
+            initialize()
+        n = int(sum(sizes))
+        h = vp()
+        _check(hostlib().sb_matrix_create_tiled(_dtype_code(dtype), HERMITIAN, ord(uplo), n, n, None, 0,
+                                                _sizes(sizes), len(sizes), p, q, ord(origin), C.byref(h)))
+        return _adopt(cls, h, n, n, max(sizes), p, q, dtype, uplo=uplo)
+
+    @classmethod
+    def fromDevices(cls, uplo, n, dev_tensor, lda, nb, p=1, q=1, dtype=np.float64):
+        if not _initialized:
+            initialize()
+        h = vp()
+        _check(hostlib().sb_matrix_from_devices(_dtype_code(dtype), HERMITIAN, ord(uplo), n, n,
+                                                dev_tensor.data_ptr(), lda, nb, p, q, C.byref(h)))
+        return _adopt(cls, h, n, n, nb, p, q, dtype, uplo=uplo, keep=dev_tensor)
 
 
 class SymmetricMatrix(HermitianMatrix):

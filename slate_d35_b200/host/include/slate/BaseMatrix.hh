@@ -58,6 +58,19 @@ protected:
         nt_ = storage_->nt_;
     }
 
+    /// include/slate/BaseMatrix.hh (lambda constructor): caller-supplied tile sizes and owners
+    BaseMatrix(int64_t m, int64_t n, std::function<int64_t(int64_t)>& inTileMb,
+               std::function<int64_t(int64_t)>& inTileNb, std::function<int(ij_tuple)>& inTileRank,
+               std::function<int(ij_tuple)>& inTileDevice, MPI_Comm comm)
+        : ioffset_(0), joffset_(0), uplo_(Uplo::General), op_(Op::NoTrans),
+          layout_(Layout::ColMajor), origin_(Target::Host),
+          storage_(std::make_shared<MatrixStorage<scalar_t>>(m, n, inTileMb, inTileNb, inTileRank,
+                                                             inTileDevice, comm))
+    {
+        mt_ = storage_->mt_;
+        nt_ = storage_->nt_;
+    }
+
     /// sub-matrix view of tiles [i1..i2] x [j1..j2] (include/slate/BaseMatrix.hh:863-905)
     BaseMatrix(BaseMatrix const& orig, int64_t i1, int64_t i2, int64_t j1, int64_t j2)
         : BaseMatrix(orig)
@@ -838,6 +851,7 @@ void BaseMatrix<scalar_t>::bcastPeer(std::vector<BcastOp> const& plan)
 
     // roots: tiles valid on the device, ColMajor, the comm stream behind their producers
     std::vector<char> prepared(plan.size(), 0);
+    std::map<size_t, void*> packed_src;
     for (auto const& m : sends)
         for (size_t o : m.ops) {
             if (prepared[o]) continue;
@@ -847,6 +861,16 @@ void BaseMatrix<scalar_t>::bcastPeer(std::vector<BcastOp> const& plan)
             auto& node = storage_->at(globalIndex(i, j));
             if (node.dev->layout() != Layout::ColMajor) tileLayoutConvert(i, j, 0, Layout::ColMajor, -1);
             eng.comm_wait_queue_seq(node.write_queue, node.write_seq);
+            if (!node.dev->isContiguous()) {
+                // a user-owned device tile inside a larger array (Matrix::fromDevices): packed
+                // into a pool block first, the peer copies are one-dimensional
+                Tile<scalar_t>* t = node.dev;
+                void* packed = storage_->allocScratchBlock();
+                slate_te_call(te_memcpy2d_async(packed, sizeof(scalar_t) * t->mb(), t->data(),
+                                                sizeof(scalar_t) * t->stride(), sizeof(scalar_t) * t->mb(),
+                                                t->nb(), TE_COPY_D2D, stream));
+                packed_src[o] = packed;
+            }
         }
     // destinations: workspace tiles, stamped with the mark at the end of this call
     std::vector<Tile<scalar_t>*> dst_tile(plan.size(), nullptr);
@@ -880,15 +904,15 @@ void BaseMatrix<scalar_t>::bcastPeer(std::vector<BcastOp> const& plan)
                 run_bytes = 0;
             };
             for (size_t t = ch.first; t < ch.last; ++t) {
-                Tile<scalar_t>* tile = storage_->at(globalIndex(plan[sends[s].ops[t]].i, plan[sends[s].ops[t]].j)).dev;
+                const size_t o = sends[s].ops[t];
+                Tile<scalar_t>* tile = storage_->at(globalIndex(plan[o].i, plan[o].j)).dev;
                 const size_t b = tile->bytes();
-                if (!tile->isContiguous())
-                    slate_error("broadcast: strided device tile (user-owned device tiles must have stride == mb)");
-                const bool joins = run_bytes && run_src + run_bytes == (const char*)tile->data()
-                                   && run_off + run_bytes == o_off;
+                auto pk = packed_src.find(o);
+                const char* src = pk == packed_src.end() ? (const char*)tile->data() : (const char*)pk->second;
+                const bool joins = run_bytes && run_src + run_bytes == src && run_off + run_bytes == o_off;
                 if (!joins) {
                     flush();
-                    run_src = (const char*)tile->data();
+                    run_src = src;
                     run_off = o_off;
                 }
                 run_bytes += b;
@@ -916,6 +940,8 @@ void BaseMatrix<scalar_t>::bcastPeer(std::vector<BcastOp> const& plan)
         }
     }
     eng.trace_end(-1);
+    for (auto& kv : packed_src) storage_->freeDeferred(kv.second);
+    if (!packed_src.empty()) storage_->flushErased();
     eng.mark_comm();
     device_copies_pending_ = false;
 }

@@ -22,6 +22,37 @@ public:
            MPI_Comm comm)
         : BaseMatrix<scalar_t>(m, n, mb, nb, order, p, q, comm) {}
 
+    /// include/slate/Matrix.hh:33-38: tile sizes, owners and devices from the caller's functions
+    /// (the tester's --nonuniform-nb / --dev-order paths, test/matrix_utils.cc:15-88).  Tile
+    /// sizes need not be uniform: every kernel takes per-tile m, n, k, ld.
+    Matrix(int64_t m, int64_t n, std::function<int64_t(int64_t)>& inTileMb,
+           std::function<int64_t(int64_t)>& inTileNb, std::function<int(ij_tuple)>& inTileRank,
+           std::function<int(ij_tuple)>& inTileDevice, MPI_Comm comm)
+        : BaseMatrix<scalar_t>(m, n, inTileMb, inTileNb, inTileRank, inTileDevice, comm) {}
+
+    /// include/slate/Matrix.hh:102-112: tiles are views into the caller's DEVICE arrays, one
+    /// array per device of this rank holding that device's share of the 2D block-cyclic local
+    /// matrix in column-major order with leading dimension lda.  One GPU per process here, so
+    /// num_devices must be 1 and Aarray[0] is the rank's whole local array (ScaLAPACK layout, on
+    /// the device).  The tiles are UserOwned: never freed, results land in the caller's memory.
+    static Matrix fromDevices(int64_t m, int64_t n, scalar_t** Aarray, int num_devices, int64_t lda,
+                              int64_t mb, int64_t nb, int p, int q, MPI_Comm comm)
+    {
+        slate_assert(num_devices == 1 && Aarray != nullptr);
+        Matrix M(m, n, mb, nb, GridOrder::Col, p, q, comm);
+        M.origin_ = Target::Devices;
+        for (int64_t j = 0; j < M.nt(); ++j)
+            for (int64_t i = 0; i < M.mt(); ++i)
+                if (M.tileIsLocal(i, j))
+                    M.tileInsert(i, j, 0, &Aarray[0][(i / p) * mb + (j / q) * nb * lda], lda);
+        return M;
+    }
+    static Matrix fromDevices(int64_t m, int64_t n, scalar_t** Aarray, int num_devices, int64_t lda,
+                              int64_t nb, int p, int q, MPI_Comm comm)
+    {
+        return fromDevices(m, n, Aarray, num_devices, lda, nb, nb, p, q, comm);
+    }
+
     /// include/slate/Matrix.hh:355-384: view of a column-major host array; every rank
     /// passes its own array and owns the tiles the grid assigns to it.
     static Matrix fromLAPACK(int64_t m, int64_t n, scalar_t* A, int64_t lda, int64_t nb,
@@ -133,6 +164,15 @@ protected:
         slate_assert(uplo == Uplo::Lower || uplo == Uplo::Upper);
         this->uplo_ = uplo;
     }
+    BaseTrapezoidMatrix(Uplo uplo, int64_t m, int64_t n, std::function<int64_t(int64_t)>& inTileMb,
+                        std::function<int64_t(int64_t)>& inTileNb,
+                        std::function<int(ij_tuple)>& inTileRank,
+                        std::function<int(ij_tuple)>& inTileDevice, MPI_Comm comm)
+        : BaseMatrix<scalar_t>(m, n, inTileMb, inTileNb, inTileRank, inTileDevice, comm)
+    {
+        slate_assert(uplo == Uplo::Lower || uplo == Uplo::Upper);
+        this->uplo_ = uplo;
+    }
     BaseTrapezoidMatrix(BaseMatrix<scalar_t> const& orig, int64_t i1, int64_t i2)
         : BaseMatrix<scalar_t>(orig, i1, i2, i1, i2) {}
     BaseTrapezoidMatrix(Uplo uplo, BaseMatrix<scalar_t> const& orig) : BaseMatrix<scalar_t>(orig)
@@ -170,6 +210,27 @@ public:
         : BaseTrapezoidMatrix<scalar_t>(uplo, n, n, nb, p, q, comm) {}
     HermitianMatrix(Uplo uplo, int64_t n, int64_t nb, GridOrder order, int p, int q, MPI_Comm comm)
         : BaseTrapezoidMatrix<scalar_t>(uplo, n, n, nb, order, p, q, comm) {}
+
+    /// HermitianMatrix.hh (lambda constructor): square, tile sizes inTileNb in both dimensions
+    HermitianMatrix(Uplo uplo, int64_t n, std::function<int64_t(int64_t)>& inTileNb,
+                    std::function<int(ij_tuple)>& inTileRank, std::function<int(ij_tuple)>& inTileDevice,
+                    MPI_Comm comm)
+        : BaseTrapezoidMatrix<scalar_t>(uplo, n, n, inTileNb, inTileNb, inTileRank, inTileDevice, comm) {}
+
+    /// HermitianMatrix.hh fromDevices: the stored triangle as views into the caller's device
+    /// array (see Matrix::fromDevices)
+    static HermitianMatrix fromDevices(Uplo uplo, int64_t n, scalar_t** Aarray, int num_devices,
+                                       int64_t lda, int64_t nb, int p, int q, MPI_Comm comm)
+    {
+        slate_assert(num_devices == 1 && Aarray != nullptr);
+        HermitianMatrix M(uplo, n, nb, p, q, comm);
+        M.origin_ = Target::Devices;
+        for (int64_t j = 0; j < M.nt(); ++j)
+            for (int64_t i = 0; i < M.mt(); ++i)
+                if (M.tileIsLocal(i, j) && M.inStoredTriangle(i, j))
+                    M.tileInsert(i, j, 0, &Aarray[0][(i / p) * nb + (j / q) * nb * lda], lda);
+        return M;
+    }
 
     /// HermitianMatrix.hh fromScaLAPACK (used by scalapack_api/*.cc)
     static HermitianMatrix fromScaLAPACK(Uplo uplo, int64_t n, scalar_t* A, int64_t lda, int64_t nb,

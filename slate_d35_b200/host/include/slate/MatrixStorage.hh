@@ -12,6 +12,7 @@
 #include "slate/Tile.hh"
 #include "slate/engine.hh"
 
+#include <algorithm>
 #include <functional>
 #include <map>
 #include <memory>
@@ -68,9 +69,48 @@ public:
         tileDevice = [](ij_tuple) { return 0; };
     }
 
+    /// include/slate/internal/MatrixStorage.hh (lambda constructor, used by Matrix.hh:33-38): tile
+    /// extents, owners and devices given by the caller's functions; tile sizes need not be
+    /// uniform.  The pool's block holds the largest tile.  One GPU per process: inTileDevice is
+    /// kept for the interface and must map local tiles to device 0.
+    MatrixStorage(int64_t m, int64_t n, std::function<int64_t(int64_t)>& inTileMb,
+                  std::function<int64_t(int64_t)>& inTileNb, std::function<int(ij_tuple)>& inTileRank,
+                  std::function<int(ij_tuple)>& inTileDevice, Comm* comm)
+        : m_(m), n_(n), mb_(largest_tile(m, inTileMb)), nb_(largest_tile(n, inTileNb)),
+          mt_(count_tiles(m, inTileMb)), nt_(count_tiles(n, inTileNb)), order_(GridOrder::Unknown),
+          p_(-1), q_(-1), comm_(comm), tileMb(inTileMb), tileNb(inTileNb), tileRank(inTileRank),
+          tileDevice(inTileDevice),
+          memory_(sizeof(scalar_t) * (size_t)std::max<int64_t>(mb_, 1) * (size_t)std::max<int64_t>(nb_, 1))
+    {
+        slate_assert(comm != nullptr);
+    }
+
     ~MatrixStorage()
     {
         try { clear(); } catch (...) {}
+    }
+
+    static int64_t count_tiles(int64_t extent, std::function<int64_t(int64_t)>& size_of)
+    {
+        int64_t t = 0;
+        for (int64_t ii = 0; ii < extent; ++t) {
+            const int64_t s = size_of(t);
+            slate_assert(s > 0);
+            ii += s;
+            slate_assert(ii <= extent);        // the tile sizes must add up to the extent
+        }
+        return t;
+    }
+    static int64_t largest_tile(int64_t extent, std::function<int64_t(int64_t)>& size_of)
+    {
+        int64_t t = 0, big = 0;
+        for (int64_t ii = 0; ii < extent; ++t) {
+            const int64_t s = size_of(t);
+            slate_assert(s > 0);
+            big = std::max(big, s);
+            ii += s;
+        }
+        return big;
     }
 
     // ---- lookups ----

@@ -7,6 +7,8 @@
 #include "slate/slate.hh"
 
 #include <cstring>
+#include <functional>
+#include <vector>
 #include <memory>
 #include <string>
 
@@ -225,6 +227,76 @@ int sb_matrix_create(int dtype, int kind, int uplo, int diag, int64_t m, int64_t
         h->kind = kind;
         if (dtype == TE_C64) create<zdouble>(h.get(), kind, uplo, diag, m, n, nb, p, q, origin, (zdouble*)host, ld);
         else create<double>(h.get(), kind, uplo, diag, m, n, nb, p, q, origin, (double*)host, ld);
+        *out = h.release();
+    });
+}
+
+/// Lambda-constructed matrix (include/slate/Matrix.hh:33-38, HermitianMatrix.hh): tile sizes from
+/// the arrays `row_sizes` (mt entries, general matrices only) and `col_sizes` (nt entries; both
+/// dimensions of a Hermitian matrix), owners 2D block-cyclic over p x q (column-major ranks),
+/// tiles SLATE-owned on the device ('D') or the host ('H').  kind: General or Hermitian.
+int sb_matrix_create_tiled(int dtype, int kind, int uplo, int64_t m, int64_t n, const int64_t* row_sizes,
+                           int64_t mt, const int64_t* col_sizes, int64_t nt, int p, int q, int origin,
+                           void** out)
+{
+    return guarded([&] {
+        auto h = std::make_unique<Handle>();
+        h->dtype = dtype;
+        h->kind = kind;
+        std::vector<int64_t> rs(row_sizes ? row_sizes : col_sizes, (row_sizes ? row_sizes + mt : col_sizes + nt));
+        std::vector<int64_t> cs(col_sizes, col_sizes + nt);
+        std::function<int64_t(int64_t)> tmb = [rs](int64_t i) { return i < (int64_t)rs.size() ? rs[i] : 1; };
+        std::function<int64_t(int64_t)> tnb = [cs](int64_t j) { return j < (int64_t)cs.size() ? cs[j] : 1; };
+        std::function<int(ij_tuple)> trank = func::process_2d_grid(GridOrder::Col, p, q);
+        std::function<int(ij_tuple)> tdev = [](ij_tuple) { return 0; };
+        MPI_Comm comm = MPI_COMM_WORLD;
+        if (p * q == 1 && comm->size > 1) comm = MPI_COMM_SELF;
+        const Target org = (origin == 'D') ? Target::Devices : Target::Host;
+        auto build = [&](auto tag) {
+            using T = decltype(tag);
+            if (kind == Hermitian) {
+                auto M = std::make_shared<HermitianMatrix<T>>(uplo == 'U' ? Uplo::Upper : Uplo::Lower, n, tnb,
+                                                              trank, tdev, comm);
+                M->insertLocalTiles(org);
+                h->obj = M;
+            }
+            else if (kind == General) {
+                auto M = std::make_shared<Matrix<T>>(m, n, tmb, tnb, trank, tdev, comm);
+                M->insertLocalTiles(org);
+                h->obj = M;
+            }
+            else slate_error("sb_matrix_create_tiled: General or Hermitian only");
+        };
+        if (dtype == TE_C64) build(zdouble());
+        else build(double());
+        *out = h.release();
+    });
+}
+
+/// Matrix::fromDevices / HermitianMatrix::fromDevices (include/slate/Matrix.hh:102-112): tiles are
+/// views into the caller's device array `dev` (this rank's 2D block-cyclic local matrix, column
+/// major, leading dimension lda).
+int sb_matrix_from_devices(int dtype, int kind, int uplo, int64_t m, int64_t n, void* dev, int64_t lda,
+                           int64_t nb, int p, int q, void** out)
+{
+    return guarded([&] {
+        auto h = std::make_unique<Handle>();
+        h->dtype = dtype;
+        h->kind = kind;
+        MPI_Comm comm = MPI_COMM_WORLD;
+        if (p * q == 1 && comm->size > 1) comm = MPI_COMM_SELF;
+        auto build = [&](auto tag) {
+            using T = decltype(tag);
+            T* arr[1] = {(T*)dev};
+            if (kind == Hermitian)
+                h->obj = std::make_shared<HermitianMatrix<T>>(HermitianMatrix<T>::fromDevices(
+                    uplo == 'U' ? Uplo::Upper : Uplo::Lower, n, arr, 1, lda, nb, p, q, comm));
+            else if (kind == General)
+                h->obj = std::make_shared<Matrix<T>>(Matrix<T>::fromDevices(m, n, arr, 1, lda, nb, p, q, comm));
+            else slate_error("sb_matrix_from_devices: General or Hermitian only");
+        };
+        if (dtype == TE_C64) build(zdouble());
+        else build(double());
         *out = h.release();
     });
 }

@@ -329,6 +329,11 @@ int64_t potrf(HermitianMatrix<scalar_t>& A_in, Options const& opts)
         ~ShortCtaGuard() { if (on_) te_gemm_set_items_per_cta(0); }
         bool on_;
     } short_cta_guard(A.mpiComm()->size > 1);
+    static const bool tail_policy_env = [] {
+        const char* e = std::getenv("SLATE_B200_POTRF_TAIL_CAP");
+        return !(e && e[0] == '0');
+    }();
+    const bool tail_policy = tail_policy_env && A.mpiComm()->size > 1;
 
     // info of step k stays on the device (the reference copies it back and syncs each step)
     slate_te_call(te_memset_async(eng.info_slot(0), 0, sizeof(int) * A_nt,
@@ -372,6 +377,14 @@ int64_t potrf(HermitianMatrix<scalar_t>& A_in, Options const& opts)
 
         // ---- trailing submatrix (src/potrf.cc:136-149) ----
         if (k + 1 + lookahead < A_nt) {
+            if (tail_policy) {
+                // Late in the factorisation the update is shorter than the panel chain that
+                // runs beside it: then what matters is how soon the chain's kernels find a free
+                // SM, i.e. how short the update's CTAs are, not the update's own L2 locality.
+                const int64_t r = A_nt - (k + 1 + lookahead);
+                const int64_t local_tiles = r * (r + 1) / 2 / A.mpiComm()->size;
+                te_gemm_set_items_per_cta(local_tiles < 300 ? 1 : local_tiles < 800 ? 2 : 4);
+            }
             internal::herk<Target::Devices>(real_t(-1.0), A.sub(k + 1 + lookahead, A_nt - 1, k, k),
                                             real_t(1.0), A.sub(k + 1 + lookahead, A_nt - 1), 0,
                                             queue_trail, layout);
