@@ -45,7 +45,6 @@ constexpr int NPRODUCERS = 4;                      //                 producer w
 constexpr int NTHREADS = (NCONSUMERS + NPRODUCERS) * 32;
 constexpr int REGS_PRODUCER = 56;                  // setmaxnreg budgets: 56*P + 224*C = 168*(P+C)
 constexpr int REGS_CONSUMER = 224;                 //   for C = 2P consumer / producer threads
-constexpr int LD_K = KC + 4;             // row stride (doubles) of an [mn][k] slice
 
 // Shape of the real kernel.  Two are built:
 //   Wide      128x128 CTA tile, 8 consumer + 4 producer warps, 5-stage ring, ONE CTA per SM
@@ -64,8 +63,10 @@ constexpr int LD_K = KC + 4;             // row stride (doubles) of an [mn][k] s
 // producer "warpgroup" had only two warps hung in setmaxnreg: the instruction is specified per
 // group of four warps.)
 template <int BN_, int NCONS_, int NPROD_, int STAGES_, int CTAS_PER_SM_, int NIDLE_ = 0,
-          int REGS_C_ = REGS_CONSUMER, int REGS_P_ = REGS_PRODUCER>
+          int REGS_C_ = REGS_CONSUMER, int REGS_P_ = REGS_PRODUCER, int KC_ = KC>
 struct DCfg {
+    static constexpr int KCv = KC_;              // K extent of one ring slice
+    static constexpr int LD_Kv = KC_ + 4;        // row stride (doubles) of an [mn][k] slice
     static constexpr int BNv = BN_;
     static constexpr int NCONS = NCONS_;
     static constexpr int NPROD = NPROD_;
@@ -76,8 +77,8 @@ struct DCfg {
     static constexpr int THREADS = (NCONS_ + NPROD_ + NIDLE_) * 32;
     static constexpr int LD_A = BM + 4;      // row stride (doubles) of a [k][m] slice of A
     static constexpr int LD_B = BN_ + 4;     //                         a [k][n] slice of B
-    static constexpr int SLICE_A = (KC * LD_A > BM * LD_K) ? KC * LD_A : BM * LD_K;
-    static constexpr int SLICE_B = (KC * LD_B > BN_ * LD_K) ? KC * LD_B : BN_ * LD_K;
+    static constexpr int SLICE_A = (KC_ * LD_A > BM * LD_Kv) ? KC_ * LD_A : BM * LD_Kv;
+    static constexpr int SLICE_B = (KC_ * LD_B > BN_ * LD_Kv) ? KC_ * LD_B : BN_ * LD_Kv;
     static constexpr int SMEM = STAGES_ * (SLICE_A + SLICE_B) * (int)sizeof(double) + 2 * STAGES_ * 8;
     static_assert(NCONS_ == 2 * (BN_ / 32), "consumer warps tile the block as 2 (m) x BN/32 (n)");
     // registers per thread at launch (multiple of 8) and the pool setmaxnreg redistributes
@@ -86,6 +87,11 @@ struct DCfg {
                   "setmaxnreg budget");
 };
 using CfgWide = DCfg<128, 8, 4, 5, 1>;
+// Wide32 (the default): K slices of 32 in a 3-stage ring (221 KB): half as many full / empty
+// barrier hand-offs per block (ncu: they were ~4.7 % of the consumers' K-loop samples with
+// slices of 16).  Measured on one B200 against Wide: 33.08 vs 32.85 TFLOP/s at n = 65536
+// (12 steps), 32.39 vs 31.7 at the 2x4 grid's launch shape.
+using CfgWide32 = DCfg<128, 8, 4, 3, 1, 0, REGS_CONSUMER, REGS_PRODUCER, 32>;
 // PairFull: two idle warps complete the producer warpgroup (setmaxnreg is specified per
 // warpgroup of four warps); they give their registers back and exit.  256 threads per CTA,
 // 128 registers per thread at launch, so the consumers get 200 instead of 224.
@@ -160,7 +166,7 @@ __device__ __forceinline__ bool decode(const GemmParams& p, int64_t w, Item& it)
 // tiles), which keeps the A / B tiles they share resident in L2; giving each CTA a
 // contiguous run instead spread the SMs over 148 different tiles and cost 1.6x more
 // DRAM reads (ncu, profiles/).
-template <bool INL, int BMv = 128, int BNv = 128>
+template <bool INL, int BMv = 128, int BNv = 128, int KCv = KC>
 struct Walker {
     int64_t w;
     int left;      // items this CTA may still take
@@ -175,7 +181,7 @@ struct Walker {
         while (left > 0 && w < p.total_work) {
             if (decode<INL, BMv, BNv>(p, w, it)) {
                 valid = true;
-                nk = (it.k + KC - 1) / KC;
+                nk = (it.k + KCv - 1) / KCv;
                 return;
             }
             w += stride;
@@ -203,12 +209,14 @@ struct Walker {
 // extents from there (anything beyond is zero-filled).
 //   KMAJOR == false: global (x, kk) at g[x + kk*ld]  -> smem [kk][LD_MN]
 //   KMAJOR == true : global (x, kk) at g[kk + x*ld]  -> smem [x][LD_K]
-template <bool KMAJOR, int X, int LD_MNv, int NPROD>
+template <bool KMAJOR, int X, int LD_MNv, int NPROD, int KCv>
 __device__ __forceinline__ void load_slice(double* s, const double* g, int ld,
                                            int x_rem, int k_rem, bool al16, int ptid)
 {
     const uint32_t sbase = smem_u32(s);
-    constexpr int NCHUNK = X * KC / 2;           // 16-byte chunks per slice
+    constexpr int LD_K = KCv + 4;
+    constexpr int KHALF = KCv / 2;               // chunks per row of an [mn][k] slice
+    constexpr int NCHUNK = X * KCv / 2;          // 16-byte chunks per slice
     constexpr int HALF = X / 2;                  // chunks per k row of an [k][mn] slice
 #pragma unroll
     for (int i = 0; i < NCHUNK / (NPROD * 32); ++i) {
@@ -222,8 +230,8 @@ __device__ __forceinline__ void load_slice(double* s, const double* g, int ld,
             soff = (uint32_t)(row * LD_MNv + col);
         }
         else {
-            row = c >> 3;              // x
-            col = (c & 7) * 2;         // kk
+            row = c / KHALF;           // x
+            col = (c % KHALF) * 2;     // kk
             nv = (row < x_rem) ? min(max(k_rem - col, 0), 2) : 0;
             soff = (uint32_t)(row * LD_K + col);
         }
@@ -250,6 +258,8 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::CTAS_PER_SM)
 dgemm_tiles_kernel(const __grid_constant__ GemmParams p)
 {
     constexpr int STAGES = Cfg::STAGES;
+    constexpr int KC = Cfg::KCv;                 // (shadows the file-scope value)
+    constexpr int LD_K = Cfg::LD_Kv;
     constexpr int NCONSUMERS = Cfg::NCONS;       // (shadow the file-scope values of the complex kernel)
     constexpr int NPRODUCERS = Cfg::NPROD;
     constexpr int BN = Cfg::BNv;
@@ -279,7 +289,7 @@ dgemm_tiles_kernel(const __grid_constant__ GemmParams p)
     constexpr bool A_KMAJOR = TA;
     constexpr bool B_KMAJOR = !TB;
 
-    Walker<INL, BM, BN> wk;
+    Walker<INL, BM, BN, KC> wk;
     wk.start(p);
     int stage = 0;
     uint32_t phase = 0;
@@ -315,8 +325,8 @@ dgemm_tiles_kernel(const __grid_constant__ GemmParams p)
                         ? it.b + (int64_t)it.n0 * it.ldb + k0
                         : it.b + (int64_t)k0 * it.ldb + it.n0;
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
-                    load_slice<A_KMAJOR, BM, LD_MN_A, NPRODUCERS>(sA + stage * SLICE_A, ga, it.lda, it.m, k_rem, it.a16, ptid);
-                    load_slice<B_KMAJOR, BN, LD_MN_B, NPRODUCERS>(sB + stage * SLICE_B, gb, it.ldb, it.n, k_rem, it.b16, ptid);
+                    load_slice<A_KMAJOR, BM, LD_MN_A, NPRODUCERS, KC>(sA + stage * SLICE_A, ga, it.lda, it.m, k_rem, it.a16, ptid);
+                    load_slice<B_KMAJOR, BN, LD_MN_B, NPRODUCERS, KC>(sB + stage * SLICE_B, gb, it.ldb, it.n, k_rem, it.b16, ptid);
                     cp_async_mbar_arrive(full0 + 8 * stage);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -756,14 +766,14 @@ static int dispatch(int device, cudaStream_t stream, int opa, int opb, const Gem
     return launch<true, true, INL, Cfg>(device, stream, p);
 }
 
-// Which shape the real kernel runs in: 0 wide (default), 2 two CTAs per SM
-// (TE_DGEMM_SHAPE=wide|pairfull; see DCfg).
+// Which shape the real kernel runs in: 3 wide with K slices of 32 (default), 0 wide with K slices
+// of 16, 2 two CTAs per SM (TE_DGEMM_SHAPE=wide32|wide|pairfull; see DCfg).
 static int dgemm_shape()
 {
     static int choice = -1;
     if (choice < 0) {
         const char* e = getenv("TE_DGEMM_SHAPE");
-        choice = (e && strcmp(e, "pairfull") == 0) ? 2 : 0;
+        choice = (e && strcmp(e, "pairfull") == 0) ? 2 : (e && strcmp(e, "wide") == 0) ? 0 : 3;
     }
     return choice;
 }
@@ -783,10 +793,14 @@ template <bool INL>
 static int dgemm_launch_shape(int device, cudaStream_t stream, int opa, int opb, GemmParams& p,
                               int64_t count, int32_t max_m, int32_t max_n, bool wide)
 {
-    const int shape = wide ? 0 : dgemm_shape();
+    const int shape = (wide && dgemm_shape() == 2) ? 0 : dgemm_shape();
     if (shape == 2) {
         shape_params<CfgPairFull>(device, p, count, max_m, max_n);
         return dispatch<INL, CfgPairFull>(device, stream, opa, opb, p);
+    }
+    if (shape == 3) {
+        shape_params<CfgWide32>(device, p, count, max_m, max_n);
+        return dispatch<INL, CfgWide32>(device, stream, opa, opb, p);
     }
     shape_params<CfgWide>(device, p, count, max_m, max_n);
     return dispatch<INL, CfgWide>(device, stream, opa, opb, p);
