@@ -385,6 +385,25 @@ int te_tile_transpose_batch(int device, void* stream, int dtype, int conj, int m
 int te_tile_symmetrize(int device, void* stream, int dtype, int uplo, int hermitian, int n, void* A,
                        int64_t lda);
 
+/* Panel <-> tiles.  Host-origin tiles that are neighbours in the caller's array cross PCIe as
+ * ONE copy into / out of a device panel (column-major, leading dimension ld_panel elements);
+ * this call moves the pieces between the panel and the tiles' own device blocks: to_tiles != 0
+ * panel -> tiles, else tiles -> panel.  pieces_host is a HOST array (it travels in the kernel
+ * parameters, TE_MAX_PANEL_PIECES per launch).  Stands in for the per-tile copies of
+ * Tile::copyData (include/slate/Tile.hh:971-1042) inside BaseMatrix::tileGetAllForWritingOnDevices /
+ * tileUpdateAllOrigin (include/slate/BaseMatrix.hh:3081-3243): one host<->device copy costs the
+ * enqueueing thread ~21 us whatever its size, so a slab of 2048 tiles cost 43 ms per direction. */
+#define TE_MAX_PANEL_PIECES 96
+typedef struct te_panel_piece {
+    void*   tile;            /* device block of the tile                               */
+    int64_t panel_offset;    /* element offset of the piece inside the panel           */
+    int32_t m, n;            /* extents of the piece                                   */
+    int32_t ld;              /* leading dimension of the tile block, elements          */
+    int32_t reserved;
+} te_panel_piece;            /* 32 bytes */
+int te_panel_pieces(int device, void* stream, int dtype, int to_tiles, void* panel,
+                    int64_t ld_panel, const te_panel_piece* pieces_host, int count);
+
 int te_tile_sumsq(int device, void* stream, int dtype, int mask, int m, int n, const void* A,
                   int64_t lda, double* accum_dev);
 int te_tile_keep_triangle(int device, void* stream, int dtype, int uplo, int m, int n, void* A,

@@ -204,3 +204,74 @@ extern "C" int te_tile_keep_triangle(int device, void* stream, int dtype, int up
     TE_CUDA_CHECK(cudaGetLastError());
     return TE_OK;
 }
+
+// ---------------------------------------------------------------- panel <-> tiles
+// A run of host-origin tiles that lie next to each other in the caller's array (a block column
+// of a ScaLAPACK-layout local matrix: tiles stacked in rows; a block row: tiles side by side)
+// crosses PCIe as ONE copy into / out of a device panel; these kernels move the panel's pieces
+// to / from the tiles' own blocks.  Why: every cudaMemcpy(2D)Async between host and device costs
+// the enqueueing host thread ~21 us whatever its size (scripts/copy_batch_probe.py), so
+// fetching a slab of 2048 tiles one by one took 43 ms of host time per direction and the host,
+// not PCIe, set the pace of the host-origin gemm.
+namespace te {
+struct PanelPieces {
+    te_panel_piece piece[TE_MAX_PANEL_PIECES];
+    int count;
+};
+
+// blockIdx.x = piece, blockIdx.y = slice of its columns.  d = doubles per element.
+template <bool TO_TILES>
+__global__ void panel_pieces_kernel(double* __restrict__ panel, int64_t ld_panel, int d, const __grid_constant__ PanelPieces pp)
+{
+    const te_panel_piece& pc = pp.piece[blockIdx.x];
+    const int64_t rows = (int64_t)pc.m * d;                // doubles per column
+    double* tile = (double*)pc.tile;
+    const int64_t ldt = (int64_t)pc.ld * d;
+    double* pan = panel + pc.panel_offset * d;
+    const int64_t ldp = ld_panel * d;
+    const bool vec = ((rows | ldt | ldp) & 1) == 0 && (((uintptr_t)tile | (uintptr_t)pan) & 15) == 0;
+    for (int j = blockIdx.y; j < pc.n; j += gridDim.y) {
+        double* t = tile + (int64_t)j * ldt;
+        double* q = pan + (int64_t)j * ldp;
+        if (vec) {
+            for (int64_t i = threadIdx.x; i < rows / 2; i += blockDim.x) {
+                if (TO_TILES) reinterpret_cast<double2*>(t)[i] = reinterpret_cast<const double2*>(q)[i];
+                else reinterpret_cast<double2*>(q)[i] = reinterpret_cast<const double2*>(t)[i];
+            }
+        }
+        else {
+            for (int64_t i = threadIdx.x; i < rows; i += blockDim.x) {
+                if (TO_TILES) t[i] = q[i];
+                else q[i] = t[i];
+            }
+        }
+    }
+}
+}  // namespace te
+
+extern "C" int te_panel_pieces(int device, void* stream, int dtype, int to_tiles, void* panel,
+                               int64_t ld_panel, const te_panel_piece* pieces_host, int count)
+{
+    if (!panel || count < 0 || (count > 0 && !pieces_host) || ld_panel < 1) return TE_ERR_ARG;
+    int st = te::set_device(device);
+    if (st != TE_OK) return st;
+    const int d = (dtype == TE_C64) ? 2 : 1;
+    for (int first = 0; first < count; first += TE_MAX_PANEL_PIECES) {
+        te::PanelPieces pp;
+        pp.count = count - first < TE_MAX_PANEL_PIECES ? count - first : TE_MAX_PANEL_PIECES;
+        int max_n = 1;
+        for (int i = 0; i < pp.count; ++i) {
+            pp.piece[i] = pieces_host[first + i];
+            if (pp.piece[i].m < 0 || pp.piece[i].n < 0 || !pp.piece[i].tile) return TE_ERR_ARG;
+            if (pp.piece[i].n > max_n) max_n = pp.piece[i].n;
+        }
+        dim3 grid(pp.count, max_n < 64 ? max_n : 64);
+        if (to_tiles)
+            te::panel_pieces_kernel<true><<<grid, 128, 0, (cudaStream_t)stream>>>((double*)panel, ld_panel, d, pp);
+        else
+            te::panel_pieces_kernel<false><<<grid, 128, 0, (cudaStream_t)stream>>>((double*)panel, ld_panel, d, pp);
+        te::count_launch();
+        TE_CUDA_CHECK(cudaGetLastError());
+    }
+    return TE_OK;
+}

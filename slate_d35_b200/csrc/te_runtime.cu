@@ -6,6 +6,8 @@
 // (reference: include/slate/internal/Memory.hh:29-101, src/core/Memory.cc:17-218),
 // so that the host C++ above it needs no CUDA header.
 #include "te_common.cuh"
+#include <string.h>
+#include <stdlib.h>
 #include <mutex>
 #include <vector>
 

@@ -283,16 +283,26 @@ public:
     /// BaseMatrix.hh:3081-3104 (fetch_C in gemmC.cc:70-74)
     void tileGetAllForWritingOnDevices(LayoutConvert = LayoutConvert::None, int queue = -1)
     {
-        for (int64_t j = 0; j < nt(); ++j)
-            for (int64_t i = 0; i < mt(); ++i)
-                if (tileIsLocal(i, j) && inStoredTriangle(i, j)) tileGet(i, j, 0, true, queue);
-        finishSet(0, queue);
+        tileGetAllOnDevices(true, queue);
     }
     void tileGetAllForReadingOnDevices(LayoutConvert = LayoutConvert::None, int queue = -1)
     {
-        for (int64_t j = 0; j < nt(); ++j)
-            for (int64_t i = 0; i < mt(); ++i)
-                if (tileIsLocal(i, j) && inStoredTriangle(i, j)) tileGet(i, j, 0, false, queue);
+        tileGetAllOnDevices(false, queue);
+    }
+    /// block column by block column: local tiles that are neighbours in the caller's host array
+    /// travel as one copy (tileGetRun)
+    void tileGetAllOnDevices(bool modify, int queue)
+    {
+        std::vector<std::pair<int64_t, int64_t>> run;
+        const bool by_column = (op_ == Op::NoTrans);
+        for (int64_t a = 0; a < (by_column ? nt() : mt()); ++a) {
+            run.clear();
+            for (int64_t b = 0; b < (by_column ? mt() : nt()); ++b) {
+                const int64_t i = by_column ? b : a, j = by_column ? a : b;
+                if (tileIsLocal(i, j) && inStoredTriangle(i, j)) run.push_back({i, j});
+            }
+            tileGetRun(run, modify, queue);
+        }
         finishSet(0, queue);
     }
 
@@ -306,17 +316,28 @@ public:
     /// its tile); a later tileUpdateAllOrigin() / Engine::sync_all() completes them.
     void tileUpdateAllOriginAsync()
     {
-        for (int64_t j = 0; j < nt(); ++j)
-            for (int64_t i = 0; i < mt(); ++i)
-                if (tileIsLocal(i, j) && inStoredTriangle(i, j) && tileExists(i, j)) updateOrigin(i, j);
+        updateAllOrigin();
         host_copies_pending_ = false;
     }
     void tileUpdateAllOrigin()
     {
-        for (int64_t j = 0; j < nt(); ++j)
-            for (int64_t i = 0; i < mt(); ++i)
-                if (tileIsLocal(i, j) && inStoredTriangle(i, j) && tileExists(i, j)) updateOrigin(i, j);
+        updateAllOrigin();
         finishHostCopies();
+    }
+    /// block column by block column (of the stored matrix): neighbours in the caller's host
+    /// array go home as one copy (updateOriginRun)
+    void updateAllOrigin()
+    {
+        std::vector<std::pair<int64_t, int64_t>> run;
+        const bool by_column = (op_ == Op::NoTrans);
+        for (int64_t a = 0; a < (by_column ? nt() : mt()); ++a) {
+            run.clear();
+            for (int64_t b = 0; b < (by_column ? mt() : nt()); ++b) {
+                const int64_t i = by_column ? b : a, j = by_column ? a : b;
+                if (tileIsLocal(i, j) && inStoredTriangle(i, j) && tileExists(i, j)) run.push_back({i, j});
+            }
+            updateOriginRun(run);
+        }
     }
 
     // ---- workspace -----------------------------------------------------------------------
@@ -558,6 +579,21 @@ protected:
 
     void tileGet(int64_t i, int64_t j, int device, bool modify, int queue);
     void updateOrigin(int64_t i, int64_t j);
+    /// tileGet(.., device 0, ..) / updateOrigin for a list of tiles in the order they lie in the
+    /// caller's host array; neighbours cross PCIe as ONE copy through a device panel
+    void tileGetRun(std::vector<std::pair<int64_t, int64_t>> const& tiles, bool modify, int queue);
+    void updateOriginRun(std::vector<std::pair<int64_t, int64_t>> const& tiles);
+    /// roots of a broadcast plan: their host-origin tiles are fetched run by run
+    void fetchRootRuns(std::vector<BcastOp> const& plan, int me);
+    /// 1: b lies right below a in the same host array (block column); 2: right of it (block
+    /// row); 0: neither
+    static int hostNeighbours(Tile<scalar_t> const* a, Tile<scalar_t> const* b)
+    {
+        if (a->stride() != b->stride()) return 0;
+        if (a->nb() == b->nb() && b->data() == a->data() + a->mb()) return 1;
+        if (a->mb() == b->mb() && b->data() == a->data() + (int64_t)a->nb() * a->stride()) return 2;
+        return 0;
+    }
     void bcastCoalesced(std::vector<BcastOp> const& plan);
     void bcastPeer(std::vector<BcastOp> const& plan);
     Tile<scalar_t>* prepareToReceive(int64_t i, int64_t j);
@@ -693,6 +729,199 @@ void BaseMatrix<scalar_t>::updateOrigin(int64_t i, int64_t j)
 }
 
 //------------------------------------------------------------------------------
+/// Host -> device for tiles in host-memory order.  Maximal runs of neighbours (same host
+/// array: a block column's tiles stacked in rows, or a block row's side by side) are moved by
+/// one host-to-device copy into a panel on the comm stream and spread to the tiles' blocks by
+/// te_panel_pieces; single tiles, tiles already valid on the device and tiles without a valid
+/// host instance take tileGet.  Why: each host<->device copy costs the enqueueing thread ~21 us
+/// whatever its size, which made the host the bottleneck of the host-origin gemm.
+template <typename scalar_t>
+void BaseMatrix<scalar_t>::tileGetRun(std::vector<std::pair<int64_t, int64_t>> const& tiles,
+                                      bool modify, int queue)
+{
+    Engine& eng = Engine::instance();
+    const int dtype = is_complex ? TE_C64 : TE_F64;
+    const size_t es = sizeof(scalar_t);
+    const size_t max_panel = (size_t)512 << 20;
+    auto node_of = [&](size_t t) { return storage_->find(globalIndex(tiles[t].first, tiles[t].second)); };
+    auto eligible = [&](size_t t) {
+        auto* nd = node_of(t);
+        return nd && nd->host && nd->host_state != MOSI::Invalid && nd->host->op() == Op::NoTrans
+               && !(nd->dev && nd->dev_state != MOSI::Invalid)
+               && !(nd->dev && nd->dev->kind() == TileKind::UserOwned);
+    };
+    size_t t = 0;
+    while (t < tiles.size()) {
+        if (!eligible(t)) {
+            tileGet(tiles[t].first, tiles[t].second, 0, modify, queue);
+            ++t;
+            continue;
+        }
+        // extend the run while the next tile is the same kind of neighbour
+        size_t e = t + 1;
+        int kind = 0;
+        size_t bytes = node_of(t)->host->bytes();
+        while (e < tiles.size() && e - t < TE_MAX_PANEL_PIECES && eligible(e)) {
+            const int k = hostNeighbours(node_of(e - 1)->host, node_of(e)->host);
+            if (k == 0 || (kind != 0 && k != kind)) break;
+            if (bytes + node_of(e)->host->bytes() > max_panel) break;
+            kind = k;
+            bytes += node_of(e)->host->bytes();
+            ++e;
+        }
+        if (e - t < 2) {
+            tileGet(tiles[t].first, tiles[t].second, 0, modify, queue);
+            ++t;
+            continue;
+        }
+        Tile<scalar_t>* first = node_of(t)->host;
+        // panel: kind 1 = (sum of mb) x nb, kind 2 = mb x (sum of nb); column major, tight
+        int64_t ext = 0;
+        for (size_t u = t; u < e; ++u) ext += (kind == 1) ? node_of(u)->host->mb() : node_of(u)->host->nb();
+        const int64_t ld_panel = (kind == 1) ? ext : first->mb();
+        const int64_t panel_cols = (kind == 1) ? first->nb() : ext;
+        Engine::CommSlab& slab = eng.acquire_slab(false, (size_t)ld_panel * panel_cols * es);
+        slate_te_call(te_memcpy2d_async(slab.dev, es * ld_panel, first->data(), es * first->stride(),
+                                        es * ld_panel, panel_cols, TE_COPY_H2D, eng.comm_stream()));
+        std::vector<te_panel_piece> pieces;
+        int64_t off = 0;
+        for (size_t u = t; u < e; ++u) {
+            const ij_tuple gij = globalIndex(tiles[u].first, tiles[u].second);
+            auto& node = storage_->at(gij);
+            if (!node.dev) storage_->tileInsert(gij, 0, TileKind::Workspace);
+            Tile<scalar_t>* d = node.dev;
+            if (d->layout() != Layout::ColMajor) d->setLayout(Layout::ColMajor, d->mb());
+            te_panel_piece pc;
+            pc.tile = d->data();
+            pc.panel_offset = (kind == 1) ? off : off * ld_panel;
+            pc.m = (int32_t)d->mb();
+            pc.n = (int32_t)d->nb();
+            pc.ld = (int32_t)d->stride();
+            pc.reserved = 0;
+            pieces.push_back(pc);
+            off += (kind == 1) ? d->mb() : d->nb();
+            // bookkeeping exactly as tileGet
+            node.dev_state = MOSI::Shared;
+            node.write_queue = -1;
+            node.comm_seq = eng.next_comm_seq();
+            if (node.comm_seq > needed_comm_seq_) needed_comm_seq_ = node.comm_seq;
+            if (node.host_state == MOSI::Modified) node.host_state = MOSI::Shared;
+            if (modify) {
+                node.dev_state = MOSI::Modified;
+                node.host_state = MOSI::Invalid;
+                if (queue >= 0) {
+                    node.write_queue = queue;
+                    node.write_seq = eng.next_queue_seq(queue);
+                }
+            }
+        }
+        slate_te_call(te_panel_pieces(eng.device(), eng.comm_stream(), dtype, 1, slab.dev, ld_panel,
+                                      pieces.data(), (int)pieces.size()));
+        eng.retire_slab(false, slab);
+        device_copies_pending_ = true;
+        t = e;
+    }
+}
+
+//------------------------------------------------------------------------------
+/// Device -> host (updateOrigin) for tiles in host-memory order: neighbours are gathered into a
+/// panel on the home stream and go home as one copy.
+template <typename scalar_t>
+void BaseMatrix<scalar_t>::updateOriginRun(std::vector<std::pair<int64_t, int64_t>> const& tiles)
+{
+    Engine& eng = Engine::instance();
+    const int dtype = is_complex ? TE_C64 : TE_F64;
+    const size_t es = sizeof(scalar_t);
+    const size_t max_panel = (size_t)512 << 20;
+    auto node_of = [&](size_t t) { return storage_->find(globalIndex(tiles[t].first, tiles[t].second)); };
+    auto eligible = [&](size_t t) {
+        auto* nd = node_of(t);
+        return nd && nd->host && nd->host->origin() && nd->host_state == MOSI::Invalid
+               && nd->host->op() == Op::NoTrans && nd->dev && nd->dev_state != MOSI::Invalid
+               && nd->dev->layout() == Layout::ColMajor;
+    };
+    size_t t = 0;
+    while (t < tiles.size()) {
+        if (!eligible(t)) {
+            updateOrigin(tiles[t].first, tiles[t].second);
+            ++t;
+            continue;
+        }
+        size_t e = t + 1;
+        int kind = 0;
+        size_t bytes = node_of(t)->host->bytes();
+        while (e < tiles.size() && e - t < TE_MAX_PANEL_PIECES && eligible(e)) {
+            const int k = hostNeighbours(node_of(e - 1)->host, node_of(e)->host);
+            if (k == 0 || (kind != 0 && k != kind)) break;
+            if (bytes + node_of(e)->host->bytes() > max_panel) break;
+            kind = k;
+            bytes += node_of(e)->host->bytes();
+            ++e;
+        }
+        if (e - t < 2) {
+            updateOrigin(tiles[t].first, tiles[t].second);
+            ++t;
+            continue;
+        }
+        Tile<scalar_t>* first = node_of(t)->host;
+        int64_t ext = 0;
+        for (size_t u = t; u < e; ++u) ext += (kind == 1) ? node_of(u)->host->mb() : node_of(u)->host->nb();
+        const int64_t ld_panel = (kind == 1) ? ext : first->mb();
+        const int64_t panel_cols = (kind == 1) ? first->nb() : ext;
+        std::vector<te_panel_piece> pieces;
+        int64_t off = 0;
+        int last_q = -2;
+        uint64_t last_qseq = 0, last_cseq = 0;
+        for (size_t u = t; u < e; ++u) {
+            auto& node = *node_of(u);
+            // the home stream behind the launch that produced the tile and the comm work that
+            // filled it (one wait per distinct mark)
+            if (node.write_queue != last_q || node.write_seq > last_qseq) {
+                eng.home_wait_queue_seq(node.write_queue, node.write_seq);
+                last_q = node.write_queue;
+                last_qseq = node.write_seq;
+            }
+            if (node.comm_seq > last_cseq) {
+                eng.home_wait_comm_seq(node.comm_seq);
+                last_cseq = node.comm_seq;
+            }
+            Tile<scalar_t>* d = node.dev;
+            te_panel_piece pc;
+            pc.tile = d->data();
+            pc.panel_offset = (kind == 1) ? off : off * ld_panel;
+            pc.m = (int32_t)d->mb();
+            pc.n = (int32_t)d->nb();
+            pc.ld = (int32_t)d->stride();
+            pc.reserved = 0;
+            pieces.push_back(pc);
+            off += (kind == 1) ? d->mb() : d->nb();
+            node.host_state = MOSI::Shared;
+            if (node.dev_state == MOSI::Modified) node.dev_state = MOSI::Shared;
+        }
+        Engine::CommSlab& slab = eng.acquire_slab(true, (size_t)ld_panel * panel_cols * es);
+        slate_te_call(te_panel_pieces(eng.device(), eng.home_stream(), dtype, 0, slab.dev, ld_panel,
+                                      pieces.data(), (int)pieces.size()));
+        slate_te_call(te_memcpy2d_async(first->data(), es * first->stride(), slab.dev, es * ld_panel,
+                                        es * ld_panel, panel_cols, TE_COPY_D2H, eng.home_stream()));
+        eng.retire_slab(true, slab);
+        host_copies_pending_ = true;
+        t = e;
+    }
+}
+
+//------------------------------------------------------------------------------
+/// The tiles this rank is the root of, in plan order: consecutive ones are usually a block
+/// column (A(:, k)) or a block row (B(k, :)) of a host-origin matrix.
+template <typename scalar_t>
+void BaseMatrix<scalar_t>::fetchRootRuns(std::vector<BcastOp> const& plan, int me)
+{
+    std::vector<std::pair<int64_t, int64_t>> run;
+    for (auto const& op : plan)
+        if (op.root == me) run.push_back({op.i, op.j});
+    if (run.size() >= 2 && op_ == Op::NoTrans) tileGetRun(run, false, -1);
+}
+
+//------------------------------------------------------------------------------
 template <typename scalar_t>
 template <Target target>
 void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
@@ -705,10 +934,13 @@ void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
     if (comm->size == 1) {
         // BaseMatrix.hh:2057-2097: with one rank the "broadcast" is the fetch onto the device
         if (target == Target::Devices && num_devices() > 0) {
+            std::vector<std::pair<int64_t, int64_t>> run;
             for (auto& e : bcast_list) {
                 int64_t i = std::get<0>(e), j = std::get<1>(e);
-                if (tileIsLocal(i, j)) tileGet(i, j, 0, false, -1);
+                if (tileIsLocal(i, j)) run.push_back({i, j});
             }
+            if (op_ == Op::NoTrans) tileGetRun(run, false, -1);
+            else for (auto& ij : run) tileGet(ij.first, ij.second, 0, false, -1);
             finishSet(0, -1);
         }
         return;
@@ -727,6 +959,7 @@ void BaseMatrix<scalar_t>::listBcastMT(BcastListTag& bcast_list, Layout layout,
     }
     void* stream = eng.comm_stream();
     auto plan = bcastPlan(bcast_list);
+    fetchRootRuns(plan, me);
     // Roots first: fetching / converting a tile may itself put work and a mark on the comm
     // stream, and the receivers below are stamped with the mark that FOLLOWS the group.
     for (auto const& op : plan) {
@@ -850,6 +1083,7 @@ void BaseMatrix<scalar_t>::bcastPeer(std::vector<BcastOp> const& plan)
     for (auto const& m : recvs) { recv_chunks.push_back(cut(m)); rounds = std::max(rounds, recv_chunks.back().size()); }
 
     // roots: tiles valid on the device, ColMajor, the comm stream behind their producers
+    fetchRootRuns(plan, me);
     std::vector<char> prepared(plan.size(), 0);
     std::map<size_t, void*> packed_src;
     for (auto const& m : sends)

@@ -158,9 +158,13 @@ public:
     };
     /// A device buffer of at least `bytes` for pack / unpack copies on the comm stream; blocks
     /// only if all slabs of the ring still belong to unfinished broadcasts.
-    CommSlab& acquire_comm_slab(size_t bytes);
+    CommSlab& acquire_comm_slab(size_t bytes) { return acquire_slab(false, bytes); }
     /// Call after the last comm-stream operation that touches the slab was enqueued.
-    void retire_comm_slab(CommSlab& slab);
+    void retire_comm_slab(CommSlab& slab) { retire_slab(false, slab); }
+    /// The same for either side stream: home == false the comm stream, true the home stream
+    /// (panels of host-origin tiles on their way to / from the host, BaseMatrix::tileGetRun).
+    CommSlab& acquire_slab(bool home, size_t bytes);
+    void retire_slab(bool home, CommSlab& slab);
 
     /// Device scratch private to queue q (grows; stream-ordered reuse on that queue).
     void* scratch(int q, size_t bytes);
@@ -229,8 +233,8 @@ private:
     int* info_base_ = nullptr;
     int info_cap_ = 4096;
     static const int CommSlabs = 4;
-    CommSlab comm_slab_[CommSlabs];
-    int comm_slab_next_ = 0;
+    CommSlab comm_slab_[2][CommSlabs];       // [0] comm stream, [1] home stream
+    int comm_slab_next_[2] = {0, 0};
     std::deque<Deferred> deferred_;
     std::vector<void*> event_pool_;
     std::recursive_mutex mu_;

@@ -320,11 +320,12 @@ Engine::DescSlot& Engine::acquire_desc(int q, size_t bytes)
     return s;
 }
 
-Engine::CommSlab& Engine::acquire_comm_slab(size_t bytes)
+Engine::CommSlab& Engine::acquire_slab(bool home, size_t bytes)
 {
     std::lock_guard<std::recursive_mutex> lock(mu_);
-    CommSlab& s = comm_slab_[comm_slab_next_];
-    comm_slab_next_ = (comm_slab_next_ + 1) % CommSlabs;
+    const int w = home ? 1 : 0;
+    CommSlab& s = comm_slab_[w][comm_slab_next_[w]];
+    comm_slab_next_[w] = (comm_slab_next_[w] + 1) % CommSlabs;
     if (s.pending) {
         slate_te_call(te_event_sync(s.event));
         s.pending = false;
@@ -340,9 +341,9 @@ Engine::CommSlab& Engine::acquire_comm_slab(size_t bytes)
     return s;
 }
 
-void Engine::retire_comm_slab(CommSlab& s)
+void Engine::retire_slab(bool home, CommSlab& s)
 {
-    slate_te_call(te_event_record(s.event, comm_stream()));
+    slate_te_call(te_event_record(s.event, home ? home_stream() : comm_stream()));
     s.pending = true;
 }
 
