@@ -16,6 +16,7 @@
 #include "slate/MatrixStorage.hh"
 
 #include <algorithm>
+#include <cstdlib>
 #include <list>
 #include <map>
 #include <set>
@@ -587,6 +588,21 @@ protected:
     void fetchRootRuns(std::vector<BcastOp> const& plan, int me);
     /// 1: b lies right below a in the same host array (block column); 2: right of it (block
     /// row); 0: neither
+    /// SLATE_B200_TILE_RUNS=1 turns the panel path on (default off: every tile its own copy).
+    /// Measured with bench.py's e2e arm at 20 steps (round 2): no gain where it was expected --
+    /// 8 GPUs 137.9 against 137.4 TFLOP/s, 1 GPU 29.3 against 28.3-30.4 across boxes -- and 3 %
+    /// slower on 2 GPUs (56.0 against 57.7: the scatter / gather kernels wait for SMs the update
+    /// holds, and the tiles cross HBM twice).  The host's copy-enqueue time is real (21 us per
+    /// copy) but, once the write-backs are enqueued late (drivers.cc), it is hidden behind the
+    /// 16-deep launch queue.
+    static bool tile_runs_enabled()
+    {
+        static const bool on = [] {
+            const char* e = std::getenv("SLATE_B200_TILE_RUNS");
+            return e && e[0] == '1';
+        }();
+        return on;
+    }
     static int hostNeighbours(Tile<scalar_t> const* a, Tile<scalar_t> const* b)
     {
         if (a->stride() != b->stride()) return 0;
@@ -746,7 +762,7 @@ void BaseMatrix<scalar_t>::tileGetRun(std::vector<std::pair<int64_t, int64_t>> c
     auto node_of = [&](size_t t) { return storage_->find(globalIndex(tiles[t].first, tiles[t].second)); };
     auto eligible = [&](size_t t) {
         auto* nd = node_of(t);
-        return nd && nd->host && nd->host_state != MOSI::Invalid && nd->host->op() == Op::NoTrans
+        return tile_runs_enabled() && nd && nd->host && nd->host_state != MOSI::Invalid && nd->host->op() == Op::NoTrans
                && !(nd->dev && nd->dev_state != MOSI::Invalid)
                && !(nd->dev && nd->dev->kind() == TileKind::UserOwned);
     };
@@ -836,7 +852,7 @@ void BaseMatrix<scalar_t>::updateOriginRun(std::vector<std::pair<int64_t, int64_
     auto node_of = [&](size_t t) { return storage_->find(globalIndex(tiles[t].first, tiles[t].second)); };
     auto eligible = [&](size_t t) {
         auto* nd = node_of(t);
-        return nd && nd->host && nd->host->origin() && nd->host_state == MOSI::Invalid
+        return tile_runs_enabled() && nd && nd->host && nd->host->origin() && nd->host_state == MOSI::Invalid
                && nd->host->op() == Op::NoTrans && nd->dev && nd->dev_state != MOSI::Invalid
                && nd->dev->layout() == Layout::ColMajor;
     };

@@ -531,3 +531,47 @@ def test_posv_tester_check(sl, uplo, dt):
     B2 = sl.Matrix(n, nrhs, nb, dtype=dt).from_numpy(B0)
     sl.potrs(A, B2)
     assert np.abs(B2.to_numpy() - X).max() <= 50 * EPS * np.abs(X).max()
+
+
+def test_host_origin_tiles_through_device_panels():
+    """SLATE_B200_TILE_RUNS=1 (read once per process, hence the subprocess): host-origin tiles that
+    are neighbours in the caller's array cross PCIe as one copy through a device panel
+    (BaseMatrix::tileGetRun / updateOriginRun, te_panel_pieces).  gemm and potrf on fromLAPACK
+    arrays with padding rows, ragged tiles, against numpy."""
+    import os
+    import subprocess
+    import sys
+    code = r'''
+import numpy as np, sys, os
+sys.path.insert(0, os.path.join(os.getcwd(), "tests"))
+import oracle_lib as ol
+from slate_d35_b200 import host as sl
+eps = np.finfo(np.float64).eps
+for dtype in (np.float64, np.complex128):
+    m, n, k, nb, pad = 1100, 900, 700, 256, 7
+    bufs = [np.asfortranarray(np.full((r + pad, c), np.nan, dtype=dtype)) for r, c in ((m, k), (k, n), (m, n))]
+    A0, B0, C0 = ol.matgen(1, m, k, dtype), ol.matgen(2, k, n, dtype), ol.matgen(3, m, n, dtype)
+    for b, src in zip(bufs, (A0, B0, C0)):
+        b[:src.shape[0], :] = src
+    A = sl.Matrix.fromLAPACK(bufs[0], nb, m=m)
+    B = sl.Matrix.fromLAPACK(bufs[1], nb, m=k)
+    Cm = sl.Matrix.fromLAPACK(bufs[2], nb, m=m)
+    sl.gemm(1.5, A, B, -0.5, Cm, method="C")
+    sl.sync()
+    want = 1.5 * A0 @ B0 - 0.5 * C0
+    assert np.abs(bufs[2][:m] - want).max() / np.abs(want).max() <= 3 * np.sqrt(4 * k) * eps
+    assert np.isnan(bufs[2][m:].real).all()          # padding rows untouched
+n, nb = 1300, 256
+S0 = ol.matgen(7, n, n); S = (S0 + S0.T) / 2 + n * np.eye(n)
+buf = np.asfortranarray(np.tril(S))
+H = sl.HermitianMatrix.fromLAPACK("L", buf, nb)
+assert sl.potrf(H) == 0
+sl.sync()
+L = np.linalg.cholesky(S)
+assert np.abs(np.tril(buf) - L).max() / np.abs(L).max() <= 50 * eps
+print("PANEL PATH OK")
+'''
+    env = dict(os.environ, SLATE_B200_TILE_RUNS="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "PANEL PATH OK" in out.stdout, out.stdout[-2000:] + out.stderr[-3000:]
