@@ -684,6 +684,60 @@ zgemm_tiles_kernel(const __grid_constant__ ZParams zp)
             const bool beta_nz = (zp.br != 0.0) || (zp.bi != 0.0);
             const bool c16 = (((uintptr_t)it.c) & 15) == 0;
             double2* cblk = reinterpret_cast<double2*>(it.c) + (int64_t)it.n0 * it.ldc + it.m0;
+            const bool interior = p.use_red != 0 && (it.m >= wm + 32) && (it.n >= wn + 32) && !lower
+                                  && !upper && !herm && c16;
+            if (interior) {
+                // Whole 32x32 warp tile inside the block (as in the real kernel): no per-element
+                // tests, and no load -> use -> store chain per element.
+                double2* c0 = cblk + (int64_t)(wn + g) * it.ldc + wm + 2 * t;
+                const int64_t cstep = (int64_t)8 * it.ldc;
+                if (zp.br == 1.0 && zp.bi == 0.0) {
+                    // beta == 1: C += alpha * acc by reductions performed in L2 (no C load)
+#pragma unroll
+                    for (int in = 0; in < 4; ++in)
+#pragma unroll
+                        for (int im = 0; im < 4; ++im)
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const double ar = cre[in][im][e], ai = cim[in][im][e];
+                                double* dst = reinterpret_cast<double*>(c0 + in * cstep + im * 8 + e);
+                                asm volatile("red.global.add.f64 [%0], %1;" :: "l"(dst), "d"(zp.ar * ar - zp.ai * ai) : "memory");
+                                asm volatile("red.global.add.f64 [%0], %1;" :: "l"(dst + 1), "d"(zp.ar * ai + zp.ai * ar) : "memory");
+                            }
+                }
+                else {
+                    // half of the warp tile at a time: its 16 loads in flight before the first use
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        double2 old[2][4][2];
+                        if (beta_nz) {
+#pragma unroll
+                            for (int i2 = 0; i2 < 2; ++i2)
+#pragma unroll
+                                for (int im = 0; im < 4; ++im)
+#pragma unroll
+                                    for (int e = 0; e < 2; ++e)
+                                        old[i2][im][e] = __ldcs(c0 + (2 * h + i2) * cstep + im * 8 + e);
+                        }
+#pragma unroll
+                        for (int i2 = 0; i2 < 2; ++i2)
+#pragma unroll
+                            for (int im = 0; im < 4; ++im)
+#pragma unroll
+                                for (int e = 0; e < 2; ++e) {
+                                    const double ar = cre[2 * h + i2][im][e], ai = cim[2 * h + i2][im][e];
+                                    double vr = zp.ar * ar - zp.ai * ai;
+                                    double vi = zp.ar * ai + zp.ai * ar;
+                                    if (beta_nz) {
+                                        vr += zp.br * old[i2][im][e].x - zp.bi * old[i2][im][e].y;
+                                        vi += zp.br * old[i2][im][e].y + zp.bi * old[i2][im][e].x;
+                                    }
+                                    __stcs(c0 + (2 * h + i2) * cstep + im * 8 + e, make_double2(vr, vi));
+                                }
+                    }
+                }
+            }
+            else
 #pragma unroll
             for (int in = 0; in < 4; ++in) {
                 const int col = wn + in * 8 + g;
@@ -870,6 +924,19 @@ int dgemm_inline(int device, cudaStream_t stream, int opa, int opb, double alpha
 }
 
 
+// Interior warp tiles of the complex kernel take the branch-free epilogue the real kernel has
+// (batched C loads, reductions for beta == 1); TE_ZGEMM_EPILOGUE=0: element by element, as in
+// round 1.  Measured on one B200, zgemm n = 24576 nb = 384: 34.05 against 31.94 TFLOP/s.
+static bool zgemm_fast_epilogue()
+{
+    static int on = -1;
+    if (on < 0) {
+        const char* e = getenv("TE_ZGEMM_EPILOGUE");
+        on = (e && e[0] == '0') ? 0 : 1;
+    }
+    return on == 1;
+}
+
 template <int OPA, int OPB, bool INL>
 static int zlaunch(int device, cudaStream_t stream, const ZParams& zp)
 {
@@ -921,6 +988,7 @@ int zgemm_batched(int device, cudaStream_t stream, int opa, int opb, const doubl
     p.wave_ctas = num_sms(device);
     p.alpha = p.beta = 0.0;
     p.inline_count = 0;
+    p.use_red = zgemm_fast_epilogue() ? 1 : 0;
     zp.ar = alpha[0];  zp.ai = alpha[1];  zp.br = beta[0];  zp.bi = beta[1];
     return zdispatch<false>(device, stream, opa, opb, zp);
 }
@@ -944,6 +1012,7 @@ int zgemm_inline(int device, cudaStream_t stream, int opa, int opb, const double
     p.wave_ctas = num_sms(device);
     p.alpha = p.beta = 0.0;
     p.inline_count = count;
+    p.use_red = zgemm_fast_epilogue() ? 1 : 0;
     zp.ar = alpha[0];  zp.ai = alpha[1];  zp.br = beta[0];  zp.bi = beta[1];
     return zdispatch<true>(device, stream, opa, opb, zp);
 }
